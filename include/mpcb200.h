@@ -1,0 +1,199 @@
+/* mpcb200.h — C ABI of libmpcb200.so: batched nonlinear MPC (PANOC + L-BFGS, ALM) on B200.
+ *
+ * This is the drop-in boundary for the one hot path of panagiotou23/model-predictive-control:
+ * the NLP solve inside MPCController.__call__ (reference controller.py:51-69), which the
+ * reference hands to alpaqa's ALMSolver(StructuredPANOCLBFGSSolver) over CasADi-generated
+ * C functions f/grad_f/g/grad_g (reference main.py:25-59).  The reference's real FFI for
+ * this path is the CasADi generated-C ABI `int f(const double** arg, double** res,
+ * long long* iw, double* w, int mem)` dlopen'ed by alpaqa (main.py:54); it is per-instance
+ * and CPU-only, so it is replaced — not mirrored — by the batched entry points below.
+ *
+ * Conventions
+ *   - every data pointer is a DEVICE pointer owned by the caller (torch tensors), fp64,
+ *     row-major [B, ...]; the *_host entry points take HOST pointers and do the copies.
+ *   - every call is asynchronous on the cudaStream_t passed as `void* stream` (0 = legacy
+ *     default stream); *_host entry points synchronise before returning.
+ *   - return value: 0 = ok, negative = MPCB_E_* ; never throws.
+ *   - U is the flat decision vector [d0, δ0, d1, δ1, ...] (column-major 2×N, reference
+ *     car_dynamics.py:149-156); the road is the flat column-major centerline
+ *     [x0..xS-1, y0..yS-1] (reference main.py:113, car_dynamics.py:204).
+ */
+#ifndef MPCB200_H
+#define MPCB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPCB_VERSION 100 /* 0.1.0 */
+
+/* model_id */
+#define MPCB_MODEL_PACEJKA6 0   /* reference car_dynamics.py:93-132 / dynamics.py:67-119 */
+#define MPCB_MODEL_KINEMATIC4 1 /* reference dynamics.py:144-173 */
+
+/* road_mode: how the `road` argument is laid out */
+#define MPCB_ROAD_SHARED 0       /* road[2S]: one polyline for every instance (main.py:112-113) */
+#define MPCB_ROAD_TABLE 1        /* road[R,2S] + road_idx[B] (int32): a few road shapes shared by the batch */
+#define MPCB_ROAD_PER_INSTANCE 2 /* road[B,2S] */
+#define MPCB_ROAD_BEZIER 3       /* road[B,12]: quintic control points Px0..5,Py0..5 (bezier_curves.py:19-48),
+                                    sampled on device to S vertices at j=i/(S-1) */
+
+/* flags */
+#define MPCB_FLAG_LANE 1      /* add u_trgl + u_rbd (dpf_test.py:45-54) to every stage */
+#define MPCB_FLAG_OBST 2      /* add dnf (dpf_test.py:81-102) for n_obs obstacles to every stage */
+#define MPCB_FLAG_BOUNDED_D 4 /* state constraints g (main.py:43-52) are bounded by D_lower/D_upper */
+
+/* status: alpaqa 0.0.1 SolverStatus order (reference controller.py:64 compares against Converged) */
+#define MPCB_STATUS_UNKNOWN 0
+#define MPCB_STATUS_CONVERGED 1
+#define MPCB_STATUS_MAX_TIME 2
+#define MPCB_STATUS_MAX_ITER 3
+#define MPCB_STATUS_NOT_FINITE 4
+#define MPCB_STATUS_NO_PROGRESS 5
+#define MPCB_STATUS_INTERRUPTED 6
+
+/* error codes */
+#define MPCB_OK 0
+#define MPCB_E_ARG (-1)      /* bad argument (null pointer, size out of range) */
+#define MPCB_E_CUDA (-2)     /* CUDA runtime error; see mpcb_last_error */
+#define MPCB_E_UNSUPPORTED (-3)
+#define MPCB_E_NODEVICE (-4) /* no CUDA device: there is no CPU fallback */
+
+#define MPCB_MAX_N 64   /* horizon cap */
+#define MPCB_MAX_OBS 8  /* obstacles per instance cap */
+#define MPCB_NP 22      /* vehicle parameter vector length (car_dynamics.py:65-88) */
+#define MPCB_OBS_DIM 5  /* per obstacle: x, y, phi, v, a */
+
+/* Problem description: everything that CasADi would bake into the generated C
+ * (reference main.py:25-59, car_dynamics.py:93-147,230-258). */
+typedef struct MpcProblemDesc {
+  int32_t model_id; /* MPCB_MODEL_* */
+  int32_t N;        /* horizon length N_horiz (main.py:68; 12 in the demo) */
+  int32_t S;        /* centerline vertices (main.py:70; 100) */
+  int32_t n_sub;    /* RK4 finite elements per stage (car_dynamics.py:136; 4) */
+  int32_t road_mode;
+  int32_t n_roads;  /* R for MPCB_ROAD_TABLE */
+  int32_t flags;
+  int32_t n_obs;
+  double Ts;        /* stage length (car_dynamics.py:93; 0.05) */
+  double v_ref;     /* target speed (main.py:65; 1.0) */
+  double c[6];      /* stage-cost weights (car_dynamics.py:230): speed, cte, pos, heading, steer, drive */
+  double kin_friction; /* dynamics.py:34 (1)  — Kinematic-4 only */
+  double kin_accel;    /* dynamics.py:35 (2)  — Kinematic-4 only */
+  /* lane potentials, dpf_test.py:5,45-54 */
+  double lane_a, lane_y_t;           /* u_trgl: a (0.5), y_trgl (1.75) */
+  double lane_b, lane_y_br, lane_y_bl; /* u_rbd: b (100), y_br (1), y_bl (6) */
+  /* obstacle potential, dpf_test.py:81 */
+  double obs_Af, obs_b, obs_sigma_x, obs_sigma_y, obs_alpha_div; /* 1000, 1, 2, 0.5, 5 */
+  /* state constraints g_i = y_i^2 - g_offset[i] (main.py:46-51) and their box D */
+  double g_offset[6];
+  double D_lower[6], D_upper[6]; /* +-inf = unbounded (the reference leaves D at +-inf, main.py:57) */
+} MpcProblemDesc;
+
+/* Solver parameters: alpaqa 0.0.1 defaults with the overrides of reference controller.py:27-48.
+ * Wall-clock caps (controller.py:30,44) are deliberately absent: they make results time-dependent. */
+typedef struct MpcSolverParams {
+  /* inner: StructuredPANOCLBFGS */
+  int32_t max_iter;        /* 1000 (controller.py:31) */
+  int32_t lbfgs_mem;       /* N_horiz (controller.py:36) */
+  int32_t max_no_progress; /* 10 */
+  int32_t hess_vec_fd;     /* 1: finite-difference Hessian-vector correction on the active set */
+  double Lgamma_factor;    /* 0.95 */
+  double L_min, L_max;     /* 1e-5, 1e20 */
+  double lip_eps, lip_delta; /* 1e-6, 1e-12 */
+  double tau_min;          /* 1/256 */
+  double quad_tol;         /* 10*DBL_EPSILON: descent-lemma rounding tolerance factor */
+  double ls_tol;           /* 10*DBL_EPSILON: line-search rounding tolerance factor */
+  /* outer: ALM (controller.py:39-48) */
+  int32_t alm_max_iter;    /* 1000 */
+  int32_t reserved0;
+  double eps_target;       /* ε  = 1e-6 */
+  double delta_target;     /* δ  = 1e-4 */
+  double Sigma0;           /* Σ_0 = 1e5 */
+  double eps0;             /* ε_0 = 1 */
+  double rho;              /* ρ = 0.1 */
+  double theta;            /* θ = 0.1 */
+  double Delta;            /* Δ = 10 */
+  double M;                /* 1e9 */
+  double Sigma_max;        /* 1e9 */
+} MpcSolverParams;
+
+typedef struct MpcHandle MpcHandle;
+
+int mpcb_version(void);
+/* Fill with the reference's constants (main.py:65-86, car_dynamics.py:230, controller.py:27-48). */
+void mpcb_default_desc(MpcProblemDesc* desc, int32_t model_id, int32_t N, int32_t S);
+void mpcb_default_solver_params(MpcSolverParams* sp, int32_t N);
+/* The 22 vehicle constants of main.py:82-111 in car_dynamics.py:65-88 order. */
+void mpcb_default_vehicle_params(double* p22);
+
+int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out);
+void mpcb_destroy(MpcHandle* h);
+const char* mpcb_last_error(MpcHandle* h);
+
+/* Continuous-time model ẏ = f(y,u;p): replaces dynamics.py:67 / :144 __call__ (clip=1 mirrors
+ * clip_inputs, dynamics.py:99) and the CasADi Function `f` (car_dynamics.py:132; clip=0). */
+int mpcb_dynamics(MpcHandle* h, int64_t B, const double* x /*[B,nx]*/, const double* u /*[B,2]*/,
+                  const double* p /*[22]*/, int32_t clip, double* xdot_out /*[B,nx]*/, void* stream);
+
+/* Nearest vertex + tracking errors: replaces car_dynamics.py:174-228 (normalised=0: raw cross
+ * products, scan i=1..S-2) and road.py:36-81 (normalised=1: divided by segment length, plain argmin). */
+int mpcb_road_errors(MpcHandle* h, int64_t B, const double* pos /*[B,2]*/, const double* heading /*[B]*/,
+                     const double* road, const int32_t* road_idx, int32_t normalised,
+                     int32_t* idx_out /*[B]*/, double* err_out /*[B,3] cte, heading, pos*/, void* stream);
+
+/* Sample the Bezier road of every instance to S vertices: replaces bezier_curves.py:19-25. */
+int mpcb_bezier_sample(MpcHandle* h, int64_t B, const double* ctrl /*[B,12]*/, double* road_out /*[B,2S]*/,
+                       void* stream);
+
+/* Horizon rollout + cost: replaces model.simulate (car_dynamics.py:158-166) and the cost sum
+ * (main.py:34-40).  states_out[B,N,nx] = state AFTER each input; idx_out[B,N] nearest vertex. */
+int mpcb_rollout(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p,
+                 const double* road, const int32_t* road_idx, const double* obs /*[B,n_obs,5] or NULL*/,
+                 double* states_out, int32_t* idx_out, double* cost_out, void* stream);
+
+/* ψ and ∇_U ψ (forward rollout + reverse sweep): replaces the generated C `f` + `grad_f`
+ * (and g/grad_g through lambda/Sigma when MPCB_FLAG_BOUNDED_D; pass NULL for plain f). */
+int mpcb_value_grad(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p,
+                    const double* road, const int32_t* road_idx, const double* obs,
+                    const double* lambda /*[B,nx*N] or NULL*/, const double* Sigma /*[B,nx*N] or NULL*/,
+                    double* cost_out /*[B]*/, double* grad_out /*[B,2N]*/, void* stream);
+
+/* The MPC step's NLP solve: replaces `self.solver(problem, U, λ)` (controller.py:57).
+ * U_inout / lambda_inout carry the warm start in and the solution out (controller.py:20-21,57). */
+int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double* x0, const double* p,
+               const double* road, const int32_t* road_idx, const double* obs,
+               const double* lb /*[2N]*/, const double* ub /*[2N]*/,
+               double* U_inout /*[B,2N]*/, double* lambda_inout /*[B,nx*N]*/,
+               int32_t* status_out /*[B]*/, int32_t* iters_out /*[B,2] outer, inner*/,
+               int32_t* evals_out /*[B,2] psi-only, psi+grad*/, double* psi_out /*[B]*/,
+               double* res_out /*[B] final ||p||_2*/, void* stream);
+
+/* Same solve with HOST buffers: pinned staging, H2D, solve, D2H, synchronise.  This is the call the
+ * reference-facing controller makes for numpy inputs; road_idx/obs/lambda may be NULL. */
+int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double* x0, const double* p,
+                    const double* road, const int32_t* road_idx, const double* obs,
+                    const double* lb, const double* ub, double* U_inout, double* lambda_inout,
+                    int32_t* status_out, int32_t* iters_out, int32_t* evals_out, double* psi_out,
+                    double* res_out);
+
+/* Bytes moved by the last mpcb_solve_host call (bench.py's e2e.h2d/d2h_bytes_per_step). */
+void mpcb_last_transfer_bytes(MpcHandle* h, int64_t* h2d, int64_t* d2h);
+
+/* Plant step of the closed loop (main.py:145: model.simulate(1, y_n, u_n, param)). */
+int mpcb_plant_step(MpcHandle* h, int64_t B, const double* x /*[B,nx]*/, const double* u /*[B,2]*/,
+                    const double* p, double* x_out /*[B,nx]*/, void* stream);
+
+/* Measured FP64 FMA throughput of this device (dependent DFMA chains, all SMs), TFLOP/s:
+ * the roofline denominator bench.py reports against. */
+int mpcb_fp64_peak(double* tflops_out, double* ms_out);
+
+/* Number of kernels launched through this handle since creation (bench.py's gpu_launches). */
+int64_t mpcb_launch_count(MpcHandle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPCB200_H */

@@ -1,0 +1,457 @@
+// mpcb_api.cu — extern "C" boundary of libmpcb200.so (see include/mpcb200.h).
+// Host side only: argument checks, scratch management, kernel launches.  No CPU compute fallback:
+// every entry point fails with MPCB_E_NODEVICE / MPCB_E_CUDA when the GPU path cannot run.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include "mpcb_kernels.cuh"
+#include "mpcb_solve.cuh"
+
+using namespace mpcb;
+
+struct MpcHandle {
+  MpcProblemDesc desc;
+  KDesc kd;
+  int device = 0;
+  int num_sms = 148;
+  std::string err;
+  int64_t launches = 0;
+  int64_t h2d_bytes = 0, d2h_bytes = 0;
+  // grow-only device scratch
+  double* road_t = nullptr; size_t road_t_cap = 0;     // transposed per-instance roads [2S, ld]
+  double* ws = nullptr; size_t ws_cap = 0;             // solver / value_grad workspace
+  int32_t* wsi = nullptr; size_t wsi_cap = 0;
+  unsigned long long* queue = nullptr;
+  double* zero_lam = nullptr; size_t zero_lam_cap = 0;
+  // staging for *_host entry points
+  void* pin = nullptr; size_t pin_cap = 0;
+  void* dev = nullptr; size_t dev_cap = 0;
+  cudaStream_t own_stream = nullptr;
+};
+
+namespace {
+
+int fail(MpcHandle* h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+int cuda_fail(MpcHandle* h, cudaError_t e, const char* where) {
+  return fail(h, MPCB_E_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define CK(call)                                                  \
+  do {                                                            \
+    cudaError_t e__ = (call);                                     \
+    if (e__ != cudaSuccess) return cuda_fail(h, e__, #call);      \
+  } while (0)
+
+template <class T>
+int grow(MpcHandle* h, T** ptr, size_t* cap, size_t need_bytes, cudaStream_t st) {
+  if (need_bytes <= *cap) return 0;
+  if (*ptr) { CK(cudaStreamSynchronize(st)); CK(cudaFree(*ptr)); *ptr = nullptr; *cap = 0; }
+  size_t sz = need_bytes + need_bytes / 8;
+  CK(cudaMalloc((void**)ptr, sz));
+  *cap = sz;
+  return 0;
+}
+
+KDesc make_kdesc(const MpcProblemDesc& d) {
+  KDesc k;
+  std::memset(&k, 0, sizeof(k));
+  k.model_id = d.model_id; k.N = d.N; k.S = d.S; k.n_sub = d.n_sub;
+  k.nx = d.model_id == MPCB_MODEL_KINEMATIC4 ? 4 : 6;
+  k.n = 2 * d.N; k.m = k.nx * d.N; k.n_obs = d.n_obs; k.flags = d.flags; k.road_mode = d.road_mode;
+  k.n_roads = d.road_mode == MPCB_ROAD_TABLE ? d.n_roads : 1;
+  k.h = d.Ts / d.n_sub; k.Ts = d.Ts; k.v_ref = d.v_ref;
+  for (int i = 0; i < 6; ++i) { k.c[i] = d.c[i]; k.g_off[i] = d.g_offset[i]; k.D_lo[i] = d.D_lower[i]; k.D_hi[i] = d.D_upper[i]; }
+  k.kin_acc = d.kin_accel; k.kin_mu = d.kin_friction;
+  k.lane_a = d.lane_a; k.lane_y_t = d.lane_y_t; k.lane_b = d.lane_b; k.lane_y_br = d.lane_y_br; k.lane_y_bl = d.lane_y_bl;
+  k.obs_Af = d.obs_Af; k.obs_b = d.obs_b; k.obs_sx = d.obs_sigma_x; k.obs_sy = d.obs_sigma_y; k.obs_adiv = d.obs_alpha_div;
+  k.bounded = 0;
+  if (d.flags & MPCB_FLAG_BOUNDED_D)
+    for (int i = 0; i < k.nx; ++i)
+      if (!std::isinf(d.D_lower[i]) || !std::isinf(d.D_upper[i])) k.bounded = 1;
+  return k;
+}
+
+// Resolve the road argument for the evaluation kernels (stage in smem, or transpose to scratch).
+int prepare_road(MpcHandle* h, int64_t B, const double* road, const int32_t* road_idx, cudaStream_t st,
+                 RoadArg* ra, size_t* smem_bytes) {
+  const int S = h->kd.S;
+  ra->road_idx = nullptr; ra->ld = 0; ra->in_smem = 0; ra->R = 1; ra->road = road;
+  *smem_bytes = 0;
+  switch (h->kd.road_mode) {
+    case MPCB_ROAD_SHARED:
+      ra->in_smem = 1; ra->R = 1; *smem_bytes = (size_t)S * 16;
+      return 0;
+    case MPCB_ROAD_TABLE:
+      if (!road_idx) return fail(h, MPCB_E_ARG, "road_idx is required for MPCB_ROAD_TABLE");
+      ra->in_smem = 1; ra->R = h->kd.n_roads; ra->road_idx = road_idx;
+      *smem_bytes = (size_t)ra->R * S * 16;
+      if (*smem_bytes > 160 * 1024) return fail(h, MPCB_E_UNSUPPORTED, "road table exceeds 160 KB of shared memory");
+      return 0;
+    case MPCB_ROAD_PER_INSTANCE: {
+      int rc = grow(h, &h->road_t, &h->road_t_cap, (size_t)B * 2 * S * sizeof(double), st);
+      if (rc) return rc;
+      dim3 grid((unsigned)((B + 31) / 32), (unsigned)((2 * S + 31) / 32)), block(32, 8);
+      k_transpose_road<<<grid, block, 0, st>>>(B, 2 * S, road, h->road_t, B);
+      h->launches++;
+      ra->road = h->road_t; ra->ld = B;
+      return 0;
+    }
+    case MPCB_ROAD_BEZIER: {
+      int rc = grow(h, &h->road_t, &h->road_t_cap, (size_t)B * 2 * S * sizeof(double), st);
+      if (rc) return rc;
+      int64_t tot = B * S;
+      k_bezier_sample<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(S, B, road, h->road_t, 1, B);
+      h->launches++;
+      ra->road = h->road_t; ra->ld = B;
+      return 0;
+    }
+  }
+  return fail(h, MPCB_E_ARG, "bad road_mode");
+}
+
+template <class K>
+int set_smem(MpcHandle* h, K kernel, size_t bytes) {
+  if (bytes > 48 * 1024) CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mpcb_version(void) { return MPCB_VERSION; }
+
+void mpcb_default_desc(MpcProblemDesc* d, int32_t model_id, int32_t N, int32_t S) {
+  std::memset(d, 0, sizeof(*d));
+  d->model_id = model_id; d->N = N; d->S = S; d->n_sub = 4;   // car_dynamics.py:136
+  d->road_mode = MPCB_ROAD_SHARED; d->n_roads = 1; d->flags = 0; d->n_obs = 0;
+  d->Ts = 0.05;                                                // car_dynamics.py:93
+  d->v_ref = 1.0;                                              // main.py:65
+  const double c[6] = {0.5, 1, 1, 0.5, 0.1, 0.01};             // car_dynamics.py:230
+  for (int i = 0; i < 6; ++i) d->c[i] = c[i];
+  d->kin_friction = 1.0; d->kin_accel = 2.0;                   // dynamics.py:34-35
+  d->lane_a = 0.5; d->lane_y_t = 1.75; d->lane_b = 100.0; d->lane_y_br = 1.0; d->lane_y_bl = 6.0;  // dpf_test.py:5,45-54
+  d->obs_Af = 1000.0; d->obs_b = 1.0; d->obs_sigma_x = 2.0; d->obs_sigma_y = 0.5; d->obs_alpha_div = 5.0;  // dpf_test.py:81,91
+  const double off[6] = {20, 1, 1, 2, 1, 0.1};                 // main.py:46-51
+  const double inf = std::numeric_limits<double>::infinity();
+  for (int i = 0; i < 6; ++i) { d->g_offset[i] = off[i]; d->D_lower[i] = -inf; d->D_upper[i] = inf; }  // main.py:57
+}
+
+void mpcb_default_solver_params(MpcSolverParams* sp, int32_t N) {
+  std::memset(sp, 0, sizeof(*sp));
+  sp->max_iter = 1000; sp->lbfgs_mem = N; sp->max_no_progress = 10; sp->hess_vec_fd = 1;  // controller.py:31,36
+  sp->Lgamma_factor = 0.95; sp->L_min = 1e-5; sp->L_max = 1e20; sp->lip_eps = 1e-6; sp->lip_delta = 1e-12;
+  sp->tau_min = 1.0 / 256; sp->quad_tol = 10 * 2.220446049250313e-16; sp->ls_tol = 10 * 2.220446049250313e-16;
+  sp->alm_max_iter = 1000; sp->eps_target = 1e-6; sp->delta_target = 1e-4; sp->Sigma0 = 1e5;  // controller.py:41-45
+  sp->eps0 = 1.0; sp->rho = 0.1; sp->theta = 0.1; sp->Delta = 10.0; sp->M = 1e9; sp->Sigma_max = 1e9;
+}
+
+void mpcb_default_vehicle_params(double* p) {  // main.py:82-111
+  const double v[MPCB_NP] = {9.7e-2, 4.7e-2, 5e-2, 0.09, 0.07, 8e-2, 5.5e-2, 0.1735, 18.3e-5, 0.32, 1.0,
+                             0.268, 2.165, 3.47, 0.242, 2.38, 2.84, 0.266, 0.1, 0.1025, 0.1629, 0.0011};
+  for (int i = 0; i < MPCB_NP; ++i) p[i] = v[i];
+}
+
+int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
+  if (!desc || !out) return MPCB_E_ARG;
+  *out = nullptr;
+  if (desc->N < 1 || desc->N > MPCB_MAX_N || desc->S < 3 || desc->n_sub < 1 || desc->n_obs < 0 ||
+      desc->n_obs > MPCB_MAX_OBS || desc->model_id < 0 || desc->model_id > 1 || desc->road_mode < 0 ||
+      desc->road_mode > 3)
+    return MPCB_E_ARG;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MPCB_E_NODEVICE;
+  MpcHandle* h = new MpcHandle();
+  h->desc = *desc;
+  h->kd = make_kdesc(*desc);
+  cudaGetDevice(&h->device);
+  cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device);
+  if (cudaMalloc((void**)&h->queue, sizeof(unsigned long long)) != cudaSuccess) { delete h; return MPCB_E_CUDA; }
+  if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
+  *out = h;
+  return MPCB_OK;
+}
+
+void mpcb_destroy(MpcHandle* h) {
+  if (!h) return;
+  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wsi); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
+  if (h->pin) cudaFreeHost(h->pin);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+const char* mpcb_last_error(MpcHandle* h) { return h ? h->err.c_str() : "null handle"; }
+int64_t mpcb_launch_count(MpcHandle* h) { return h ? h->launches : 0; }
+
+int mpcb_dynamics(MpcHandle* h, int64_t B, const double* x, const double* u, const double* p, int32_t clip,
+                  double* out, void* stream) {
+  if (!h || !x || !u || !p || !out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_dynamics: bad argument");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned grid = (unsigned)((B + 127) / 128);
+  if (h->kd.model_id == MPCB_MODEL_PACEJKA6) k_dynamics<MPCB_MODEL_PACEJKA6><<<grid, 128, 0, st>>>(h->kd, B, x, u, p, clip, out);
+  else k_dynamics<MPCB_MODEL_KINEMATIC4><<<grid, 128, 0, st>>>(h->kd, B, x, u, p, clip, out);
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+int mpcb_plant_step(MpcHandle* h, int64_t B, const double* x, const double* u, const double* p, double* out,
+                    void* stream) {
+  if (!h || !x || !u || !p || !out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_plant_step: bad argument");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned grid = (unsigned)((B + 127) / 128);
+  if (h->kd.model_id == MPCB_MODEL_PACEJKA6) k_plant_step<MPCB_MODEL_PACEJKA6><<<grid, 128, 0, st>>>(h->kd, B, x, u, p, out);
+  else k_plant_step<MPCB_MODEL_KINEMATIC4><<<grid, 128, 0, st>>>(h->kd, B, x, u, p, out);
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+int mpcb_road_errors(MpcHandle* h, int64_t B, const double* pos, const double* heading, const double* road,
+                     const int32_t* road_idx, int32_t normalised, int32_t* idx_out, double* err_out, void* stream) {
+  if (!h || !pos || !heading || !road || !idx_out || !err_out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_road_errors: bad argument");
+  if (h->kd.road_mode == MPCB_ROAD_BEZIER) return fail(h, MPCB_E_UNSUPPORTED, "sample the Bezier road first (mpcb_bezier_sample)");
+  if (h->kd.road_mode == MPCB_ROAD_TABLE && !road_idx) return fail(h, MPCB_E_ARG, "road_idx required");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  k_road_errors<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(h->kd, B, pos, heading, road, road_idx, normalised, idx_out, err_out);
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+int mpcb_bezier_sample(MpcHandle* h, int64_t B, const double* ctrl, double* road_out, void* stream) {
+  if (!h || !ctrl || !road_out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_bezier_sample: bad argument");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t tot = B * h->kd.S;
+  k_bezier_sample<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(h->kd.S, B, ctrl, road_out, 0, 0);
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+int mpcb_rollout(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p, const double* road,
+                 const int32_t* road_idx, const double* obs, double* states_out, int32_t* idx_out, double* cost_out,
+                 void* stream) {
+  if (!h || !x0 || !U || !p || !road || B < 0) return fail(h, MPCB_E_ARG, "mpcb_rollout: bad argument");
+  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  RoadArg ra; size_t smem;
+  int rc = prepare_road(h, B, road, road_idx, st, &ra, &smem);
+  if (rc) return rc;
+  unsigned grid = (unsigned)((B + 127) / 128);
+  if (h->kd.model_id == MPCB_MODEL_PACEJKA6) {
+    if ((rc = set_smem(h, k_rollout<MPCB_MODEL_PACEJKA6>, smem))) return rc;
+    k_rollout<MPCB_MODEL_PACEJKA6><<<grid, 128, smem, st>>>(h->kd, B, x0, U, p, ra, obs, states_out, idx_out, cost_out);
+  } else {
+    if ((rc = set_smem(h, k_rollout<MPCB_MODEL_KINEMATIC4>, smem))) return rc;
+    k_rollout<MPCB_MODEL_KINEMATIC4><<<grid, 128, smem, st>>>(h->kd, B, x0, U, p, ra, obs, states_out, idx_out, cost_out);
+  }
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+int mpcb_value_grad(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p, const double* road,
+                    const int32_t* road_idx, const double* obs, const double* lambda, const double* Sigma,
+                    double* cost_out, double* grad_out, void* stream) {
+  if (!h || !x0 || !U || !p || !road || !cost_out || !grad_out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_value_grad: bad argument");
+  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  RoadArg ra; size_t smem;
+  int rc = prepare_road(h, B, road, road_idx, st, &ra, &smem);
+  if (rc) return rc;
+  // persistent grid: at most 8 CTAs of 128 lanes per SM; scratch is [rows, ns] lane-interleaved
+  const int block = 128;
+  int64_t max_blocks = (int64_t)h->num_sms * 8;
+  int64_t blocks = (B + block - 1) / block;
+  if (blocks > max_blocks) blocks = max_blocks;
+  int64_t ns = blocks * block;
+  const KDesc& k = h->kd;
+  size_t rows = (size_t)k.N * k.n_sub * k.nx + (size_t)k.N * k.nx;
+  if ((rc = grow(h, &h->ws, &h->ws_cap, rows * ns * sizeof(double), st))) return rc;
+  if ((rc = grow(h, &h->wsi, &h->wsi_cap, (size_t)k.N * ns * sizeof(int32_t), st))) return rc;
+  if (k.model_id == MPCB_MODEL_PACEJKA6) {
+    if ((rc = set_smem(h, k_value_grad<MPCB_MODEL_PACEJKA6>, smem))) return rc;
+    k_value_grad<MPCB_MODEL_PACEJKA6><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, h->ws, h->wsi, ns);
+  } else {
+    if ((rc = set_smem(h, k_value_grad<MPCB_MODEL_KINEMATIC4>, smem))) return rc;
+    k_value_grad<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, h->ws, h->wsi, ns);
+  }
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double* x0, const double* p,
+               const double* road, const int32_t* road_idx, const double* obs, const double* lb, const double* ub,
+               double* U, double* lambda, int32_t* status, int32_t* iters, int32_t* evals, double* psi, double* res,
+               void* stream) {
+  if (!h || !sp || !x0 || !p || !road || !lb || !ub || !U || !status || !iters || !evals || !psi || !res || B < 0)
+    return fail(h, MPCB_E_ARG, "mpcb_solve: bad argument");
+  if (sp->lbfgs_mem < 1 || sp->lbfgs_mem > 2 * MPCB_MAX_N || sp->max_iter < 0) return fail(h, MPCB_E_ARG, "mpcb_solve: bad solver params");
+  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const KDesc& k = h->kd;
+  int rc;
+  if (k.bounded && !lambda) {  // λ = 0 warm start (controller.py:21) when the caller keeps no multipliers
+    if ((rc = grow(h, &h->zero_lam, &h->zero_lam_cap, (size_t)B * k.m * sizeof(double), st))) return rc;
+    CK(cudaMemsetAsync(h->zero_lam, 0, (size_t)B * k.m * sizeof(double), st));
+    lambda = h->zero_lam;
+  }
+  RoadArg ra; size_t smem;
+  if ((rc = prepare_road(h, B, road, road_idx, st, &ra, &smem))) return rc;
+  smem += (size_t)2 * k.n * sizeof(double);
+  const int block = 128;
+  int64_t max_blocks = (int64_t)h->num_sms * 2;  // 255-register lanes: 2 CTAs of 128 per SM
+  int64_t blocks = (B + block - 1) / block;
+  if (blocks > max_blocks) blocks = max_blocks;
+  int64_t ns = blocks * block;
+  WsMap M(k.n, sp->lbfgs_mem, k.N, k.n_sub, k.nx, k.m);
+  if ((rc = grow(h, &h->ws, &h->ws_cap, (size_t)M.total * ns * sizeof(double), st))) return rc;
+  if ((rc = grow(h, &h->wsi, &h->wsi_cap, (size_t)k.N * ns * sizeof(int32_t), st))) return rc;
+  CK(cudaMemsetAsync(h->queue, 0, sizeof(unsigned long long), st));
+  SolveArgs a;
+  a.B = B; a.x0 = x0; a.p = p; a.obs = obs; a.lb = lb; a.ub = ub; a.ra = ra; a.U = U; a.lam = lambda;
+  a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res;
+  a.ws = h->ws; a.wsi = h->wsi; a.ns = ns; a.queue = h->queue;
+  if (k.model_id == MPCB_MODEL_PACEJKA6) {
+    if ((rc = set_smem(h, k_solve<MPCB_MODEL_PACEJKA6>, smem))) return rc;
+    k_solve<MPCB_MODEL_PACEJKA6><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);
+  } else {
+    if ((rc = set_smem(h, k_solve<MPCB_MODEL_KINEMATIC4>, smem))) return rc;
+    k_solve<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);
+  }
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+}  // extern "C"
+
+// ---- host-buffer entry point + FP64 peak probe ------------------------------------------------------
+namespace {
+struct Packer {
+  size_t off = 0;
+  size_t add(size_t bytes) { size_t o = off; off += (bytes + 255) & ~size_t(255); return o; }
+};
+}  // namespace
+
+extern "C" {
+
+int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double* x0, const double* p,
+                    const double* road, const int32_t* road_idx, const double* obs, const double* lb,
+                    const double* ub, double* U, double* lambda, int32_t* status, int32_t* iters, int32_t* evals,
+                    double* psi, double* res) {
+  if (!h || !sp || !x0 || !p || !road || !lb || !ub || !U || !status || !iters || !evals || !psi || !res || B < 0)
+    return fail(h, MPCB_E_ARG, "mpcb_solve_host: bad argument");
+  if (B == 0) return MPCB_OK;
+  const KDesc& k = h->kd;
+  cudaStream_t st = h->own_stream;
+  size_t road_elems = 0;
+  switch (k.road_mode) {
+    case MPCB_ROAD_SHARED: road_elems = 2 * (size_t)k.S; break;
+    case MPCB_ROAD_TABLE: road_elems = (size_t)k.n_roads * 2 * k.S; break;
+    case MPCB_ROAD_PER_INSTANCE: road_elems = (size_t)B * 2 * k.S; break;
+    case MPCB_ROAD_BEZIER: road_elems = (size_t)B * 12; break;
+  }
+  const bool has_obs = (k.flags & MPCB_FLAG_OBST) && k.n_obs > 0 && obs;
+  const bool has_idx = k.road_mode == MPCB_ROAD_TABLE && road_idx;
+  // inputs first (one H2D), in/out + outputs last (one D2H)
+  Packer pk;
+  size_t o_x0 = pk.add(sizeof(double) * B * k.nx), o_p = pk.add(sizeof(double) * MPCB_NP);
+  size_t o_road = pk.add(sizeof(double) * road_elems), o_idx = pk.add(has_idx ? sizeof(int32_t) * B : 0);
+  size_t o_obs = pk.add(has_obs ? sizeof(double) * B * k.n_obs * MPCB_OBS_DIM : 0);
+  size_t o_lb = pk.add(sizeof(double) * k.n), o_ub = pk.add(sizeof(double) * k.n);
+  size_t o_U = pk.add(sizeof(double) * B * k.n);
+  size_t o_lam = pk.add(lambda ? sizeof(double) * B * k.m : 0);
+  size_t in_end = pk.off;
+  size_t o_status = pk.add(sizeof(int32_t) * B), o_iters = pk.add(sizeof(int32_t) * 2 * B);
+  size_t o_evals = pk.add(sizeof(int32_t) * 2 * B), o_psi = pk.add(sizeof(double) * B), o_res = pk.add(sizeof(double) * B);
+  size_t total = pk.off;
+  if (total > h->pin_cap) {
+    if (h->pin) { CK(cudaStreamSynchronize(st)); CK(cudaFreeHost(h->pin)); h->pin = nullptr; h->pin_cap = 0; }
+    CK(cudaMallocHost(&h->pin, total + total / 8));
+    h->pin_cap = total + total / 8;
+  }
+  int rc;
+  if ((rc = grow(h, (char**)&h->dev, &h->dev_cap, total, st))) return rc;
+  char* hp = (char*)h->pin;
+  char* dp = (char*)h->dev;
+  std::memcpy(hp + o_x0, x0, sizeof(double) * B * k.nx);
+  std::memcpy(hp + o_p, p, sizeof(double) * MPCB_NP);
+  std::memcpy(hp + o_road, road, sizeof(double) * road_elems);
+  if (has_idx) std::memcpy(hp + o_idx, road_idx, sizeof(int32_t) * B);
+  if (has_obs) std::memcpy(hp + o_obs, obs, sizeof(double) * B * k.n_obs * MPCB_OBS_DIM);
+  std::memcpy(hp + o_lb, lb, sizeof(double) * k.n);
+  std::memcpy(hp + o_ub, ub, sizeof(double) * k.n);
+  std::memcpy(hp + o_U, U, sizeof(double) * B * k.n);
+  if (lambda) std::memcpy(hp + o_lam, lambda, sizeof(double) * B * k.m);
+  CK(cudaMemcpyAsync(dp, hp, in_end, cudaMemcpyHostToDevice, st));
+  rc = mpcb_solve(h, sp, B, (double*)(dp + o_x0), (double*)(dp + o_p), (double*)(dp + o_road),
+                  has_idx ? (int32_t*)(dp + o_idx) : nullptr, has_obs ? (double*)(dp + o_obs) : nullptr,
+                  (double*)(dp + o_lb), (double*)(dp + o_ub), (double*)(dp + o_U),
+                  lambda ? (double*)(dp + o_lam) : nullptr, (int32_t*)(dp + o_status), (int32_t*)(dp + o_iters),
+                  (int32_t*)(dp + o_evals), (double*)(dp + o_psi), (double*)(dp + o_res), st);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(hp + o_U, dp + o_U, total - o_U, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  std::memcpy(U, hp + o_U, sizeof(double) * B * k.n);
+  if (lambda) std::memcpy(lambda, hp + o_lam, sizeof(double) * B * k.m);
+  std::memcpy(status, hp + o_status, sizeof(int32_t) * B);
+  std::memcpy(iters, hp + o_iters, sizeof(int32_t) * 2 * B);
+  std::memcpy(evals, hp + o_evals, sizeof(int32_t) * 2 * B);
+  std::memcpy(psi, hp + o_psi, sizeof(double) * B);
+  std::memcpy(res, hp + o_res, sizeof(double) * B);
+  h->h2d_bytes = (int64_t)in_end;
+  h->d2h_bytes = (int64_t)(total - o_U);
+  return MPCB_OK;
+}
+
+void mpcb_last_transfer_bytes(MpcHandle* h, int64_t* h2d, int64_t* d2h) {
+  if (h2d) *h2d = h ? h->h2d_bytes : 0;
+  if (d2h) *d2h = h ? h->d2h_bytes : 0;
+}
+
+int mpcb_fp64_peak(double* tflops_out, double* ms_out) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MPCB_E_NODEVICE;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int block = 256, blocks = sms * 8, iters = 4000;
+  double* out = nullptr;
+  if (cudaMalloc((void**)&out, sizeof(double) * block * blocks) != cudaSuccess) return MPCB_E_CUDA;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    cudaEventRecord(e0);
+    k_fp64_peak<<<blocks, block>>>(out, iters);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(out); return MPCB_E_CUDA; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (rep > 0 && ms < best) best = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  double flops = 2.0 * 64.0 * iters * (double)block * blocks;
+  if (tflops_out) *tflops_out = flops / (best * 1e-3) / 1e12;
+  if (ms_out) *ms_out = best;
+  return MPCB_OK;
+}
+
+}  // extern "C"

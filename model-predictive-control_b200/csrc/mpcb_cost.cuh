@@ -1,0 +1,218 @@
+// mpcb_cost.cuh — nearest vertex, tracking errors, potentials and the stage cost (+ its gradient).
+// Reference: car_dynamics.py:174-258, road.py:22-81, dpf_test.py:45-102, event_triggered.py:26,
+// main.py:43-52 (state constraints through the augmented Lagrangian).
+#pragma once
+#include "mpcb_device.cuh"
+
+namespace mpcb {
+
+// A road as the kernels see it: x_i = xy[i*stride*2 .. ] is avoided; instead two strided views.
+//   shared-memory road: interleaved (x,y) pairs, rx = base, ry = base+1, stride 2
+//   SoA scratch road  : rx = roadT + b, ry = roadT + S*ld + b, stride ld
+struct RoadView {
+  const double* rx;
+  const double* ry;
+  int64_t stride;
+  MPCB_DEV double x(int i) const { return rx[(int64_t)i * stride]; }
+  MPCB_DEV double y(int i) const { return ry[(int64_t)i * stride]; }
+};
+
+#define MPCB_PI 3.141592653589793238462643383279502884
+
+// np.mod(a + pi, 2 pi) - pi: floor-mod via fmod + sign fix (car_dynamics.py:168-172).
+MPCB_DEV double wrap_to_pi(double a) {
+  const double two_pi = 2.0 * MPCB_PI;
+  double m = fmod(a + MPCB_PI, two_pi);
+  if (m < 0.0) m += two_pi;
+  return m - MPCB_PI;
+}
+
+// car_dynamics.py:174-192: the reference compares sqrt'ed distances with a strict '<' over
+// i = 1..S-2 starting from vertex 0.  sqrt is monotone, so the scan runs on squared distances
+// (rounded exactly like diff**2 summed: two products, one add, no FMA) and only falls back to the
+// sqrt comparison when two candidates are within a few ulp — same winner, bit for bit.
+MPCB_DEV int nearest_scan(const RoadView& r, int S, double px, double py) {
+  double dx = r.x(0) - px, dy = r.y(0) - py;
+  double m2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+  double m2lo = m2 * (1.0 - 1.8e-15);
+  int best = 0;
+#pragma unroll 4
+  for (int i = 1; i < S - 1; ++i) {
+    dx = r.x(i) - px;
+    dy = r.y(i) - py;
+    double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+    if (d2 < m2) {
+      if (d2 < m2lo || sqrt(d2) < sqrt(m2)) {
+        m2 = d2;
+        m2lo = m2 * (1.0 - 1.8e-15);
+        best = i;
+      }
+    }
+  }
+  return best;
+}
+
+// road.py:36-50: argmin over every vertex (first minimum of the sqrt'ed norms).
+MPCB_DEV int nearest_scan_numpy(const RoadView& r, int S, double px, double py) {
+  double dx = r.x(0) - px, dy = r.y(0) - py;
+  double m = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+  int best = 0;
+  for (int i = 1; i < S; ++i) {
+    dx = r.x(i) - px;
+    dy = r.y(i) - py;
+    double di = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    if (di < m) { m = di; best = i; }
+  }
+  return best;
+}
+
+struct RoadGeom {  // the three vertices the errors are built from, as difference vectors
+  double nx, ny;    // nearest
+  double wx, wy;    // nearest - previous
+  double w2x, w2y;  // next - nearest
+  double ax, ay;    // previous
+};
+
+MPCB_DEV void road_geom(const RoadView& r, int idx, RoadGeom& g) {
+  int ip = idx > 0 ? idx - 1 : 0;  // vertex 0 wins: previous = vertex 0 (car_dynamics.py:183)
+  int in = idx + 1;
+  g.nx = r.x(idx); g.ny = r.y(idx);
+  g.ax = r.x(ip); g.ay = r.y(ip);
+  g.wx = g.nx - g.ax; g.wy = g.ny - g.ay;
+  g.w2x = r.x(in) - g.nx; g.w2y = r.y(in) - g.ny;
+}
+
+// car_dynamics.py:194-228: cte, heading error, positional error (raw cross products).
+MPCB_DEV void road_errors(const RoadGeom& g, double px, double py, double phi, double* cte, double* he,
+                          double* pe) {
+  double vx = px - g.ax, vy = py - g.ay;
+  *cte = vx * g.wy - vy * g.wx;
+  *he = wrap_to_pi(atan2(g.w2y, g.w2x) - phi);
+  double v2x = px - g.nx, v2y = py - g.ny;
+  *pe = v2x * g.w2y - v2y * g.w2x;
+}
+
+// dpf_test.py:81-102, one obstacle; g4 (nullable) accumulates d/d(x, y, phi, v).
+MPCB_DEV double dnf_one(double x, double y, double phi, double v, double xo, double yo, double phio, double vo,
+                        const KDesc& d, double* g4) {
+  double s, c;
+  sincos(phi - phio, &s, &c);
+  double xi = c * xo - s * yo, yi = s * xo + c * yo;
+  double xr = c * x - s * y, yr = s * x + c * y;
+  double a = xr - xi, bb = yr - yi;
+  double al = (v - vo) / d.obs_adiv;
+  double isx2 = 1.0 / (d.obs_sx * d.obs_sx), isy2 = 1.0 / (d.obs_sy * d.obs_sy);
+  double q = 0.5 * a * a * isx2 + 0.5 * bb * bb * isy2;
+  bool b1 = d.obs_b == 1.0;
+  double qb = b1 ? q : pow(q, d.obs_b);
+  double U = d.obs_Af * exp(-qb) * exp(-al * a);
+  if (g4) {
+    double dq = b1 ? 1.0 : d.obs_b * pow(q, d.obs_b - 1.0);
+    double Ua = U * (-dq * a * isx2 - al);
+    double Ub = U * (-dq * bb * isy2);
+    g4[0] += Ua * c + Ub * s;
+    g4[1] += -Ua * s + Ub * c;
+    g4[2] += -Ua * bb + Ub * a;
+    g4[3] += -a * U / d.obs_adiv;
+  }
+  return U;
+}
+
+// Augmented-Lagrangian row: returns Sigma/2 dist^2, yhat out, err_z optional.
+MPCB_DEV double alm_row(double g, double lam, double Sig, double lo, double hi, double* yhat, double* err_z) {
+  double zeta = g + lam / Sig;
+  double pr = zeta < lo ? lo : (zeta > hi ? hi : zeta);
+  double dz = zeta - pr;
+  *yhat = Sig * dz;
+  if (err_z) *err_z = g - pr;
+  return 0.5 * Sig * dz * dz;
+}
+
+// Per-instance extras for the optional cost terms.
+struct Extras {
+  const double* obs;         // [n_obs,5] of this instance or null
+  const double* lam;         // ALM multipliers of this instance: lam[(n*nx+i)*lam_stride]
+  const double* Sig;         // ALM penalties, same indexing with sig_stride
+  int64_t lam_stride, sig_stride;
+};
+
+// Stage cost L(y_{n+1}, u_n) (car_dynamics.py:249-258) + optional terms.  With GRAD, gy[NX]/gu[2]
+// receive dL/dy, dL/du.  idx_io: forward pass writes the nearest index, reverse pass reuses it.
+template <int MODEL, bool GRAD, bool SCAN>
+MPCB_DEV double stage_cost(const KDesc& d, const RoadView& r, const Extras& ex, int n, const double* y, double ud,
+                           double udl, int* idx_io, double* gy, double* gu) {
+  constexpr int NX = ModelTraits<MODEL>::NX;
+  int idx = SCAN ? nearest_scan(r, d.S, y[0], y[1]) : *idx_io;
+  if (SCAN && idx_io) *idx_io = idx;
+  RoadGeom g;
+  road_geom(r, idx, g);
+  double cte, he, pe;
+  road_errors(g, y[0], y[1], y[2], &cte, &he, &pe);
+  double speed;
+  if constexpr (MODEL == MPCB_MODEL_KINEMATIC4) speed = y[3];
+  else speed = sqrt(y[3] * y[3] + y[4] * y[4]);
+  double dv = speed - d.v_ref;
+  double L = d.c[0] * dv * dv + d.c[1] * cte * cte + d.c[2] * pe * pe + d.c[3] * he * he + d.c[4] * udl * udl +
+             d.c[5] * ud * ud;
+  if (GRAD) {
+    double a1 = 2.0 * d.c[1] * cte, a2 = 2.0 * d.c[2] * pe;
+    gy[0] = a1 * g.wy + a2 * g.w2y;
+    gy[1] = -a1 * g.wx - a2 * g.w2x;
+    gy[2] = -2.0 * d.c[3] * he;
+    if constexpr (MODEL == MPCB_MODEL_KINEMATIC4) {
+      gy[3] = 2.0 * d.c[0] * dv;
+    } else {
+      double k = 2.0 * d.c[0] * dv / speed;  // NaN at standstill, like the reference's AD
+      gy[3] = k * y[3];
+      gy[4] = k * y[4];
+      gy[5] = 0.0;
+    }
+    gu[0] = 2.0 * d.c[5] * ud;
+    gu[1] = 2.0 * d.c[4] * udl;
+  }
+  if (d.flags & MPCB_FLAG_LANE) {
+    double dy = y[1] - d.lane_y_t;
+    L += d.lane_a * dy * dy;
+    double e = 0.0;
+    if (y[1] >= d.lane_y_bl) e = y[1] - d.lane_y_bl;
+    else if (y[1] <= d.lane_y_br) e = y[1] - d.lane_y_br;
+    L += d.lane_b * e * e;
+    if (GRAD) gy[1] += 2.0 * d.lane_a * dy + 2.0 * d.lane_b * e;
+  }
+  if ((d.flags & MPCB_FLAG_OBST) && ex.obs) {
+    double t = (double)(n + 1) * d.Ts;
+    for (int o = 0; o < d.n_obs; ++o) {
+      const double* ob = ex.obs + MPCB_OBS_DIM * o;
+      double so, co;
+      sincos(ob[2], &so, &co);
+      double s = ob[3] * t + 0.5 * ob[4] * t * t;  // event_triggered.py:26
+      double g4[4] = {0.0, 0.0, 0.0, 0.0};
+      L += dnf_one(y[0], y[1], y[2], y[3], ob[0] + s * co, ob[1] + s * so, ob[2], ob[3] + ob[4] * t, d,
+                   GRAD ? g4 : nullptr);
+      if (GRAD) { gy[0] += g4[0]; gy[1] += g4[1]; gy[2] += g4[2]; gy[3] += g4[3]; }
+    }
+  }
+  if (d.bounded && ex.lam && ex.Sig) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      double gi = y[i] * y[i] - d.g_off[i];
+      double yh;
+      L += alm_row(gi, ex.lam[(int64_t)(n * NX + i) * ex.lam_stride], ex.Sig[(int64_t)(n * NX + i) * ex.sig_stride],
+                   d.D_lo[i], d.D_hi[i], &yh, nullptr);
+      if (GRAD) gy[i] += 2.0 * yh * y[i];
+    }
+  }
+  return L;
+}
+
+// Quintic Bernstein point (bezier_curves.py:19-25).
+MPCB_DEV void bezier_point(const double* P /*[12]*/, double j, double* x, double* y) {
+  double u = 1.0 - j;
+  double u2 = u * u, u3 = u2 * u, u4 = u2 * u2, u5 = u4 * u;
+  double j2 = j * j, j3 = j2 * j, j4 = j2 * j2, j5 = j4 * j;
+  double w0 = u5, w1 = 5.0 * u4 * j, w2 = 10.0 * u3 * j2, w3 = 10.0 * u2 * j3, w4 = 5.0 * u * j4, w5 = j5;
+  *x = w0 * P[0] + w1 * P[1] + w2 * P[2] + w3 * P[3] + w4 * P[4] + w5 * P[5];
+  *y = w0 * P[6] + w1 * P[7] + w2 * P[8] + w3 * P[9] + w4 * P[10] + w5 * P[11];
+}
+
+}  // namespace mpcb
