@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""bench.py — PANOC MPC solves/sec on B200 (BASELINE.json metric), one JSON line on rank 0.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--batch B] [--horizon N]
+
+Step = one pass of the hot path over one batch: cold-start ALM/PANOC solve of `batch` independent N=20
+tracking MPCs per GPU (BASELINE config 2: 4096 instances, Pacejka-6, S=100, 2-road table; weak scaling:
+every rank solves its own `batch` instances, no data-path collective).
+
+  value    : solves/s with inputs resident in HBM (one k_solve launch per step, CUDA-event timed, max over ranks)
+  e2e      : solves/s through the reference-facing host call (numpy buffers -> mpcb_solve_host: pinned
+             staging + H2D + solve + D2H inside the timed region)
+  roofline : FP64-pipe roofline of k_solve: algorithmic flops (SURVEY §8d strict count, 3864*N per psi+grad
+             evaluation, 0.455 of that per psi-only evaluation, times the kernel's own evaluation counters)
+             / event time, against the DFMA-chain peak measured in this run (MEASURED_PEAKS.json has no FP64 entry)
+  cpu_baseline : the CPU oracle (C++ port of the same spec; alpaqa/CasADi cannot be installed) on a bounded
+             sample of the same workload, all host threads.
+--impl reference times that oracle as the reference arm.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_STAGE_GRAD = 3864.0   # forward 1758 + reverse 2106 per stage (Pacejka-6, S=100)
+VALUE_SHARE = 1758.0 / 3864.0  # a psi-only evaluation
+WEIGHTED_FLOP_PER_EVAL_N20 = 234e3  # SURVEY §8d secondary figure (libdevice DFMA-equivalents)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="mpcb200", choices=["mpcb200", "reference"])
+    ap.add_argument("--batch", type=int, default=4096, help="instances per GPU")
+    ap.add_argument("--horizon", type=int, default=20)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="oracle sample size (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(B, N):
+    return f"config2: {B} independent N={N} Pacejka-6 tracking MPCs per GPU, S=100, 2-road table, cold start"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_id):
+        self.lines, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_id), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append((time.perf_counter(), ln.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, ln in self.lines:
+            if t0 is not None and not (t0 <= ts <= t1 + 0.2):
+                continue
+            f = [x.strip() for x in ln.split(",")]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except Exception:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v == "Active":
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "power_w_max": float(max(pw)), "samples": len(sm)}
+
+
+def oracle_setup(N, S=100):
+    from oracle import oracle as orc
+    d = orc.default_desc(0, N, S)
+    d.road_mode, d.n_roads = 1, 2
+    return orc, d, orc.default_solver_params(N)
+
+
+def run_oracle(orc, d, sp, w, sample, threads=0):
+    t0 = time.perf_counter()
+    r = orc.solve(d, sp, w["x0"][:sample], w["road"], w["U0"][:sample], road_idx=w["road_idx"][:sample],
+                  threads=threads, want_times=True)
+    return time.perf_counter() - t0, r
+
+
+def cpu_sample_size(orc, d, sp, w, B, target_s=12.0):
+    """Bounded sample: about 10-30 s of CPU work per measurement, scaled from a 64-instance probe."""
+    n0 = min(64, B)
+    t, _ = run_oracle(orc, d, sp, w, n0)
+    per = t / n0
+    return int(max(n0, min(B, target_s / max(per, 1e-9))))
+
+
+def main_reference(args, rank, world):
+    if rank != 0:
+        return
+    from mpcb200 import workloads as wl
+    N, B = args.horizon, args.batch
+    orc, d, sp = oracle_setup(N)
+    w = wl.tracking_batch(B, N, 100, seed=2)
+    sample = args.cpu_sample or cpu_sample_size(orc, d, sp, w, B, target_s=6.0)
+    for _ in range(min(args.warmup, 1)):
+        run_oracle(orc, d, sp, w, min(sample, 64))
+    tt = 0.0
+    lat = []
+    for _ in range(args.steps):
+        t, r = run_oracle(orc, d, sp, w, sample)
+        tt += t
+        lat.append(np.median(r["times"]))
+    v = sample * args.steps / tt
+    line = {"impl": "reference", "metric": "PANOC MPC solves/sec", "value": v, "unit": "solves/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(B, N), "note": "alpaqa/CasADi are not installable here "
+                       "(SURVEY §8c): the reference arm is the repo's C++ oracle of the same canonical solver spec"},
+            "cpu_baseline": {"value": v, "unit": "solves/s", "cores": orc.num_threads(), "kind": "port",
+                             "sample": f"first {sample} instances of the workload per step, OpenMP dynamic over instances"},
+            "p50_solve_latency_ms": 1e3 * float(np.median(lat)),
+            "e2e": {"value": v, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main_gpu(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    import mpcb200
+    from mpcb200 import workloads as wl
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    N, B, S = args.horizon, args.batch, 100
+    K, W = args.steps, args.warmup
+    w = wl.tracking_batch(B, N, S, seed=2 + rank)  # every rank owns its own instances (weak scaling)
+    prob = mpcb200.BatchedMpc(N=N, S=S, road_mode=mpcb200.ROAD_TABLE, n_roads=2)
+    x0 = torch.tensor(w["x0"], device=dev)
+    road = torch.tensor(w["road"], device=dev)
+    ridx = torch.tensor(w["road_idx"], device=dev)
+    U0 = torch.tensor(w["U0"], device=dev)
+    Ubufs = [U0.clone() for _ in range(K + W)]  # cold start per step, allocated outside the timed region
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    peak_tflops, _ = mpcb200.fp64_peak_tflops()
+
+    # ---- device-resident arm ---------------------------------------------------------------------
+    stats = None
+    for i in range(W):
+        _, _, stats = prob.solve(x0, road, Ubufs[i], road_idx=ridx)
+    barrier()
+    gpu_id = local_rank
+    try:
+        gpu_id = "GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid)
+    except Exception:
+        pass
+    sampler = ClockSampler(gpu_id)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    l0 = prob.launch_count()
+    barrier()
+    t_wall0 = time.perf_counter()
+    all_stats = []
+    for i in range(K):
+        flush.zero_()  # L2 flush between timed iterations (not timed)
+        evs[i][0].record()
+        _, _, st = prob.solve(x0, road, Ubufs[W + i], road_idx=ridx)
+        evs[i][1].record()
+        all_stats.append(st)
+    barrier()
+    t_wall1 = time.perf_counter()
+    launches = prob.launch_count() - l0
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    clocks = sampler.stop(t_wall0, t_wall1)
+    t_dev = max_over_ranks(sum(step_ms) * 1e-3)
+    value = world * B * K / t_dev
+
+    st = all_stats[-1]
+    status = st.status.cpu().numpy()
+    n_val = float(st.evals_value.sum().item())
+    n_grad = float(st.evals_grad.sum().item())
+    flop_eval = FLOP_PER_STAGE_GRAD * N
+    alg_flops = (n_grad + VALUE_SHARE * n_val) * flop_eval
+    k_ms = float(np.mean(step_ms))
+    achieved = alg_flops / (k_ms * 1e-3) / 1e12
+    weighted = (n_grad + VALUE_SHARE * n_val) * WEIGHTED_FLOP_PER_EVAL_N20 * (N / 20.0) / (k_ms * 1e-3) / 1e12
+    alg_bytes = B * (6 * 8 + 2 * N * 8 * 2 + 4 + 4 * 4 + 2 * 8 + 4 * 4)  # x0, U in/out, road_idx, status/iters/evals, psi/res
+    roofline = {"bound": "fp64", "kernel": "k_solve<Pacejka6>", "achieved": achieved, "peak": peak_tflops,
+                "unit": "TFLOP/s", "frac": achieved / peak_tflops, "traffic": None,
+                "peak_source": "DFMA-chain probe measured in this run (mpcb_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
+                "flop_per_eval": flop_eval, "evals_grad_per_step": n_grad, "evals_value_per_step": n_val,
+                "weighted_achieved": weighted, "weighted_frac": weighted / peak_tflops,
+                "hbm": {"algorithmic_bytes_per_step": alg_bytes, "achieved_gbs": alg_bytes / (k_ms * 1e-3) / 1e9,
+                        "peak_gbs": _hbm_peak()}}
+
+    # ---- end-to-end arm: host buffers through mpcb_solve_host ---------------------------------------
+    Uh = [w["U0"].copy() for _ in range(K + 1)]
+    prob.solve_host(w["x0"], w["road"], Uh[K], road_idx=w["road_idx"])  # warm (allocates pinned staging)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        prob.solve_host(w["x0"], w["road"], Uh[i], road_idx=w["road_idx"])
+    t_e2e = time.perf_counter() - t0
+    barrier()
+    t_e2e = max_over_ranks(t_e2e)
+    h2d, d2h = prob.last_transfer_bytes()
+    launches += K
+
+    # ---- single-instance latency (the reference's deployment shape: one vehicle, one tick) ------------
+    lat1 = []
+    U1 = [U0[:1].clone() for _ in range(12)]
+    for i in range(12):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        prob.solve(x0[:1], road, U1[i], road_idx=ridx[:1])
+        b.record()
+        torch.cuda.synchronize()
+        lat1.append(a.elapsed_time(b))
+    conv = sum_over_ranks(float((status == 1).sum())) / (world * B)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        orc, d, sp = oracle_setup(N)
+        sample = args.cpu_sample or cpu_sample_size(orc, d, sp, w, B)
+        t, r = run_oracle(orc, d, sp, w, sample)
+        cpu = {"value": sample / t, "unit": "solves/s", "cores": orc.num_threads(), "kind": "port",
+               "sample": f"first {sample} instances of the same workload, OpenMP over instances",
+               "p50_solve_latency_ms": 1e3 * float(np.median(r["times"]))}
+
+    if rank == 0:
+        line = {"metric": "PANOC MPC solves/sec", "value": value, "unit": "solves/s", "n_gpus": world, "steps": K,
+                "warmup": W, "ms_per_step": 1e3 * t_dev / K, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": workload_name(B, N), "batch_per_gpu": B, "horizon": N,
+                           "l2": "flushed between timed steps (256 MiB memset, untimed)",
+                           "timing": "CUDA events per step on the launch stream, summed, max over ranks; e2e: host wall clock around the synchronous host call"},
+                "p50_solve_latency_ms": float(np.median(step_ms)), "batch_latency_note": "all instances of a control tick return together",
+                "single_instance_latency_ms_p50": float(np.median(lat1[2:])),
+                "converged_frac": conv, "inner_iterations_mean": float(st.inner_iterations.double().mean().item()),
+                "e2e": {"value": world * B * K / t_e2e, "unit": "solves/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": d2h},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _hbm_peak():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        return 6650.0  # B200_PROFILING.md fallback
+
+
+if __name__ == "__main__":
+    a = parse()
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if a.impl == "reference":
+        main_reference(a, rank, world)
+    else:
+        main_gpu(a, rank, local_rank, world)

@@ -190,6 +190,10 @@ int mpcb_plant_step(MpcHandle* h, int64_t B, const double* x /*[B,nx]*/, const d
  * the roofline denominator bench.py reports against. */
 int mpcb_fp64_peak(double* tflops_out, double* ms_out);
 
+/* Dependent-chain latencies on this device, SM cycles per op measured with one warp:
+ * [0] DFMA [1] div [2] sqrt [3] sincos [4] atan [5] atan2 [6] sin [7] one Pacejka model call. */
+int mpcb_latency_probe(double* cycles8);
+
 /* Number of kernels launched through this handle since creation (bench.py's gpu_launches). */
 int64_t mpcb_launch_count(MpcHandle* h);
 

@@ -69,6 +69,7 @@ SIGNATURES = {
     "mpcb_last_transfer_bytes": (None, [C.c_void_p, C.POINTER(_I64), C.POINTER(_I64)]),
     "mpcb_plant_step": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P]),
     "mpcb_fp64_peak": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "mpcb_latency_probe": (C.c_int, [C.POINTER(C.c_double)]),
     "mpcb_launch_count": (_I64, [C.c_void_p]),
 }
 

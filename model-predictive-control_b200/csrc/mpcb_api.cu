@@ -29,6 +29,9 @@ struct MpcHandle {
   void* pin = nullptr; size_t pin_cap = 0;
   void* dev = nullptr; size_t dev_cap = 0;
   cudaStream_t own_stream = nullptr;
+  cudaEvent_t last_ev = nullptr;  // completion of the last call that used the shared scratch
+  cudaStream_t last_stream = nullptr;
+  bool has_last = false;
 };
 
 namespace {
@@ -113,6 +116,21 @@ int prepare_road(MpcHandle* h, int64_t B, const double* road, const int32_t* roa
   return fail(h, MPCB_E_ARG, "bad road_mode");
 }
 
+// The handle's scratch (workspace, transposed roads, work queue) is shared by every call on it.
+// Calls may arrive on different streams (torch's current stream, the host entry point's own stream):
+// order a call after the previous one whenever the stream changes.
+int enter(MpcHandle* h, cudaStream_t st) {
+  if (h->has_last && h->last_stream != st) CK(cudaStreamWaitEvent(st, h->last_ev, 0));
+  return 0;
+}
+int leave(MpcHandle* h, cudaStream_t st) {
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(h->last_ev, st));
+  h->last_stream = st;
+  h->has_last = true;
+  return 0;
+}
+
 template <class K>
 int set_smem(MpcHandle* h, K kernel, size_t bytes) {
   if (bytes > 48 * 1024) CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
@@ -172,6 +190,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
   cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device);
   if (cudaMalloc((void**)&h->queue, sizeof(unsigned long long)) != cudaSuccess) { delete h; return MPCB_E_CUDA; }
   if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
+  if (cudaEventCreateWithFlags(&h->last_ev, cudaEventDisableTiming) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
   *out = h;
   return MPCB_OK;
 }
@@ -181,6 +200,7 @@ void mpcb_destroy(MpcHandle* h) {
   cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wsi); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
   if (h->pin) cudaFreeHost(h->pin);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  if (h->last_ev) cudaEventDestroy(h->last_ev);
   delete h;
 }
 
@@ -240,13 +260,15 @@ int mpcb_bezier_sample(MpcHandle* h, int64_t B, const double* ctrl, double* road
 int mpcb_rollout(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p, const double* road,
                  const int32_t* road_idx, const double* obs, double* states_out, int32_t* idx_out, double* cost_out,
                  void* stream) {
-  if (!h || !x0 || !U || !p || !road || B < 0) return fail(h, MPCB_E_ARG, "mpcb_rollout: bad argument");
-  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if (!h || B < 0) return fail(h, MPCB_E_ARG, "mpcb_rollout: bad argument");
   if (B == 0) return MPCB_OK;
+  if (!x0 || !U || !p || !road) return fail(h, MPCB_E_ARG, "mpcb_rollout: null argument");
+  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
   cudaStream_t st = (cudaStream_t)stream;
   RoadArg ra; size_t smem;
-  int rc = prepare_road(h, B, road, road_idx, st, &ra, &smem);
-  if (rc) return rc;
+  int rc;
+  if ((rc = enter(h, st))) return rc;
+  if ((rc = prepare_road(h, B, road, road_idx, st, &ra, &smem))) return rc;
   unsigned grid = (unsigned)((B + 127) / 128);
   if (h->kd.model_id == MPCB_MODEL_PACEJKA6) {
     if ((rc = set_smem(h, k_rollout<MPCB_MODEL_PACEJKA6>, smem))) return rc;
@@ -256,20 +278,21 @@ int mpcb_rollout(MpcHandle* h, int64_t B, const double* x0, const double* U, con
     k_rollout<MPCB_MODEL_KINEMATIC4><<<grid, 128, smem, st>>>(h->kd, B, x0, U, p, ra, obs, states_out, idx_out, cost_out);
   }
   h->launches++;
-  CK(cudaGetLastError());
-  return MPCB_OK;
+  return leave(h, st);
 }
 
 int mpcb_value_grad(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p, const double* road,
                     const int32_t* road_idx, const double* obs, const double* lambda, const double* Sigma,
                     double* cost_out, double* grad_out, void* stream) {
-  if (!h || !x0 || !U || !p || !road || !cost_out || !grad_out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_value_grad: bad argument");
-  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if (!h || B < 0) return fail(h, MPCB_E_ARG, "mpcb_value_grad: bad argument");
   if (B == 0) return MPCB_OK;
+  if (!x0 || !U || !p || !road || !cost_out || !grad_out) return fail(h, MPCB_E_ARG, "mpcb_value_grad: null argument");
+  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
   cudaStream_t st = (cudaStream_t)stream;
   RoadArg ra; size_t smem;
-  int rc = prepare_road(h, B, road, road_idx, st, &ra, &smem);
-  if (rc) return rc;
+  int rc;
+  if ((rc = enter(h, st))) return rc;
+  if ((rc = prepare_road(h, B, road, road_idx, st, &ra, &smem))) return rc;
   // persistent grid: at most 8 CTAs of 128 lanes per SM; scratch is [rows, ns] lane-interleaved
   const int block = 128;
   int64_t max_blocks = (int64_t)h->num_sms * 8;
@@ -288,22 +311,23 @@ int mpcb_value_grad(MpcHandle* h, int64_t B, const double* x0, const double* U, 
     k_value_grad<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, h->ws, h->wsi, ns);
   }
   h->launches++;
-  CK(cudaGetLastError());
-  return MPCB_OK;
+  return leave(h, st);
 }
 
 int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double* x0, const double* p,
                const double* road, const int32_t* road_idx, const double* obs, const double* lb, const double* ub,
                double* U, double* lambda, int32_t* status, int32_t* iters, int32_t* evals, double* psi, double* res,
                void* stream) {
-  if (!h || !sp || !x0 || !p || !road || !lb || !ub || !U || !status || !iters || !evals || !psi || !res || B < 0)
-    return fail(h, MPCB_E_ARG, "mpcb_solve: bad argument");
+  if (!h || !sp || B < 0) return fail(h, MPCB_E_ARG, "mpcb_solve: bad argument");
+  if (B == 0) return MPCB_OK;
+  if (!x0 || !p || !road || !lb || !ub || !U || !status || !iters || !evals || !psi || !res)
+    return fail(h, MPCB_E_ARG, "mpcb_solve: null argument");
   if (sp->lbfgs_mem < 1 || sp->lbfgs_mem > 2 * MPCB_MAX_N || sp->max_iter < 0) return fail(h, MPCB_E_ARG, "mpcb_solve: bad solver params");
   if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
-  if (B == 0) return MPCB_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const KDesc& k = h->kd;
   int rc;
+  if ((rc = enter(h, st))) return rc;
   if (k.bounded && !lambda) {  // λ = 0 warm start (controller.py:21) when the caller keeps no multipliers
     if ((rc = grow(h, &h->zero_lam, &h->zero_lam_cap, (size_t)B * k.m * sizeof(double), st))) return rc;
     CK(cudaMemsetAsync(h->zero_lam, 0, (size_t)B * k.m * sizeof(double), st));
@@ -333,8 +357,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     k_solve<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);
   }
   h->launches++;
-  CK(cudaGetLastError());
-  return MPCB_OK;
+  return leave(h, st);
 }
 
 }  // extern "C"
@@ -354,7 +377,7 @@ int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const do
                     const double* ub, double* U, double* lambda, int32_t* status, int32_t* iters, int32_t* evals,
                     double* psi, double* res) {
   if (!h || !sp || !x0 || !p || !road || !lb || !ub || !U || !status || !iters || !evals || !psi || !res || B < 0)
-    return fail(h, MPCB_E_ARG, "mpcb_solve_host: bad argument");
+    if (!(h && sp && B == 0)) return fail(h, MPCB_E_ARG, "mpcb_solve_host: bad argument");
   if (B == 0) return MPCB_OK;
   const KDesc& k = h->kd;
   cudaStream_t st = h->own_stream;
@@ -421,6 +444,20 @@ int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const do
 void mpcb_last_transfer_bytes(MpcHandle* h, int64_t* h2d, int64_t* d2h) {
   if (h2d) *h2d = h ? h->h2d_bytes : 0;
   if (d2h) *d2h = h ? h->d2h_bytes : 0;
+}
+
+/* Dependent-chain latencies (SM cycles per op, one warp): [0] DFMA [1] div [2] sqrt [3] sincos [4] atan
+ * [5] atan2 [6] sin [7] one Pacejka model call.  Diagnostic for DESIGN.md / profiles/. */
+int mpcb_latency_probe(double* cycles8) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MPCB_E_NODEVICE;
+  double* out = nullptr;
+  if (cudaMalloc((void**)&out, sizeof(double) * 64) != cudaSuccess) return MPCB_E_CUDA;
+  k_latency_probe<<<1, 32>>>(out, 0.37, 2000);
+  k_latency_probe<<<1, 32>>>(out, 0.37, 2000);
+  cudaError_t e = cudaMemcpy(cycles8, out, sizeof(double) * 8, cudaMemcpyDeviceToHost);
+  cudaFree(out);
+  return e == cudaSuccess ? MPCB_OK : MPCB_E_CUDA;
 }
 
 int mpcb_fp64_peak(double* tflops_out, double* ms_out) {

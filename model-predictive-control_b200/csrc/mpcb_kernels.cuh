@@ -201,6 +201,42 @@ k_value_grad(KDesc d, int64_t B, const double* __restrict__ x0, const double* __
   }
 }
 
+// ---- dependent-chain latency probe (one warp): cycles per DFMA / div / sqrt / sincos / atan / atan2 ----
+__global__ void k_latency_probe(double* out, double seed, int iters) {
+  double x = seed + threadIdx.x * 1e-3;
+  long long t0, t1;
+  auto tic = [&]() { __syncwarp(); t0 = clock64(); };
+  auto toc = [&](int slot) { t1 = clock64(); if (threadIdx.x == 0) out[slot] = (double)(t1 - t0) / iters; __syncwarp(); };
+  tic(); for (int i = 0; i < iters; ++i) x = fma(x, 0.999999, 1e-7); toc(0);
+  tic(); for (int i = 0; i < iters; ++i) x = 1.0 / (x + 1.5); toc(1);
+  tic(); for (int i = 0; i < iters; ++i) x = sqrt(x + 1.5); toc(2);
+  tic(); for (int i = 0; i < iters; ++i) { double s, c; sincos(x, &s, &c); x = s + 0.5 * c; } toc(3);
+  tic(); for (int i = 0; i < iters; ++i) x = atan(x * 1.3 + 0.2); toc(4);
+  tic(); for (int i = 0; i < iters; ++i) x = atan2(x + 0.1, 1.0 + 0.3 * x); toc(5);
+  tic(); for (int i = 0; i < iters; ++i) x = sin(x * 1.1); toc(6);
+  // one Pacejka model call in a dependent chain
+  {
+    __shared__ VehP v;
+    if (threadIdx.x == 0) {
+      v.lf = 4.7e-2; v.lr = 5e-2; v.m = 0.1735; v.iz = 18.3e-5; v.inv_m = 1 / 0.1735; v.inv_iz = 1 / 18.3e-5;
+      v.cm1 = 0.266; v.cm2 = 0.1; v.cr0 = 0.1025; v.cr2 = 0.0011; v.bf = 0.268; v.cf = 2.165; v.df = 3.47;
+      v.br = 0.242; v.cr = 2.38; v.dr = 2.84;
+    }
+    __syncwarp();
+    StageU su; su.d = 0.5; su.dl = 0.1; sincos(0.1, &su.sdl, &su.cdl);
+    double y[6] = {0, 0, 0.1 * x, 1.0, 0.01, 0.1}, o[6];
+    tic();
+    for (int i = 0; i < iters; ++i) {
+      pacejka_f(y, su, v, o);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) y[k] = fma(1e-4, o[k], y[k]);
+    }
+    toc(7);
+    x += y[0] + y[3] + y[5];
+  }
+  out[8 + threadIdx.x] = x;
+}
+
 // ---- FP64 FMA-chain peak probe ---------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters) {
   double a0 = 1.0 + threadIdx.x * 1e-9, a1 = a0 + 0.1, a2 = a0 + 0.2, a3 = a0 + 0.3;

@@ -27,7 +27,7 @@ def road_table(S=100):
     return np.stack([flat_F(get_centerline(S, True)), flat_F(get_centerline(S, False))])
 
 
-def tracking_batch(B, N=20, S=100, seed=2, lateral=0.05, model="pacejka", random_U=False):
+def tracking_batch(B, N=20, S=100, seed=2, lateral=0.05, model="pacejka", random_U=False, d_min=-1.0):
     """Config 2: B independent tracking instances on a 2-road table.
 
     Returns dict(x0 [B,nx], road [2,2S], road_idx [B] int32, U0 [B,2N])."""
@@ -56,7 +56,7 @@ def tracking_batch(B, N=20, S=100, seed=2, lateral=0.05, model="pacejka", random
         x0 = np.stack([pos_x, pos_y, phi, vx], axis=1)
     if random_U:
         U0 = np.empty((B, 2 * N))
-        U0[:, 0::2] = rng.uniform(-1, 1, (B, N))
+        U0[:, 0::2] = rng.uniform(d_min, 1, (B, N))  # d_min > 0 keeps vx out of the stiff low-speed regime
         U0[:, 1::2] = rng.uniform(-0.32, 0.32, (B, N))
     else:
         U0 = np.tile([1.0, 0.0], (B, N))  # controller.py:20
