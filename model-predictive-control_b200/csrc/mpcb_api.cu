@@ -300,15 +300,15 @@ int mpcb_value_grad(MpcHandle* h, int64_t B, const double* x0, const double* U, 
   if (blocks > max_blocks) blocks = max_blocks;
   int64_t ns = blocks * block;
   const KDesc& k = h->kd;
-  size_t rows = (size_t)k.N * k.n_sub * k.nx + (size_t)k.N * k.nx;
+  size_t rows = (size_t)k.N * (k.model_id == MPCB_MODEL_PACEJKA6 ? fm_stage_doubles<MPCB_MODEL_PACEJKA6>()
+                                                                   : fm_stage_doubles<MPCB_MODEL_KINEMATIC4>());
   if ((rc = grow(h, &h->ws, &h->ws_cap, rows * ns * sizeof(double), st))) return rc;
-  if ((rc = grow(h, &h->wsi, &h->wsi_cap, (size_t)k.N * ns * sizeof(int32_t), st))) return rc;
   if (k.model_id == MPCB_MODEL_PACEJKA6) {
     if ((rc = set_smem(h, k_value_grad<MPCB_MODEL_PACEJKA6>, smem))) return rc;
-    k_value_grad<MPCB_MODEL_PACEJKA6><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, h->ws, h->wsi, ns);
+    k_value_grad<MPCB_MODEL_PACEJKA6><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, h->ws, ns);
   } else {
     if ((rc = set_smem(h, k_value_grad<MPCB_MODEL_KINEMATIC4>, smem))) return rc;
-    k_value_grad<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, h->ws, h->wsi, ns);
+    k_value_grad<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, h->ws, ns);
   }
   h->launches++;
   return leave(h, st);

@@ -19,9 +19,53 @@
 #define MPCB_FM_FN inline
 #endif
 
+// How device code gets polynomial coefficients (sm_100a DFMA takes register, uniform-register or
+// 32-bit-immediate operands only): 0 = literals (two UMOV each), 1 = __constant__ tables,
+// 2 = one shared-memory table filled by fm_load_smem() at kernel start.  Measured with
+// tools/ubench_model.cu; see profiles/r01_ubench_model.json.
+#ifndef MPCB_FM_MODE
+#define MPCB_FM_MODE 0
+#endif
+#if defined(__CUDACC__)
+#define MPCB_FM_TABLE(name, n, ...)                  \
+  static const double name##_h[n] = {__VA_ARGS__};   \
+  static __constant__ double name##_d[n] = {__VA_ARGS__};
+#else
+#define MPCB_FM_TABLE(name, n, ...) static const double name##_h[n] = {__VA_ARGS__};
+#endif
+#if !defined(__CUDA_ARCH__)
+#define MPCB_FM_C(name) name##_h
+#elif MPCB_FM_MODE == 2
+#define MPCB_FM_C(name) (fm_smem + name##_off)
+#else
+#define MPCB_FM_C(name) name##_d
+#endif
+
 namespace mpcb {
 
+#if defined(__CUDACC__) && MPCB_FM_MODE == 2
+static __shared__ double fm_smem[64];
+#endif
+
 #include "mpcb_fastmath_coef.h"
+
+#if defined(__CUDACC__)
+// Mode 2: every kernel that uses the fm_* functions calls this once (all threads) before them.
+__device__ __forceinline__ void fm_load_smem() {
+#if MPCB_FM_MODE == 2
+  for (int i = threadIdx.x; i < MPCB_FM_SMEM_DOUBLES; i += blockDim.x) {
+    double v;
+    if (i < fm_c_atan_full_off) v = fm_c_atan_small_d[i];
+    else if (i < fm_c_sin_off) v = fm_c_atan_full_d[i - fm_c_atan_full_off];
+    else if (i < fm_c_cos_off) v = fm_c_sin_d[i - fm_c_sin_off];
+    else if (i < fm_c_misc_off) v = fm_c_cos_d[i - fm_c_cos_off];
+    else v = fm_c_misc_d[i - fm_c_misc_off];
+    fm_smem[i] = v;
+  }
+  __syncthreads();
+#endif
+}
+#endif
 
 // 1/x to <= 1 ulp: MUFU seed (20 bits, measured 9.9e-7) + one third-order correction (3 DFMA).
 // Finite non-zero normal x only (callers guard).
@@ -47,9 +91,9 @@ MPCB_FM_FN int fm_lo32(double v) {
 #endif
 }
 
-// sin and cos of x.  Cody-Waite reduction with three FMA (valid for |x| < 1e5), 7-term kernels.
+// sin and cos of x.  Cody-Waite reduction with three FMA (valid for |x| < 2^17), 7-term kernels.
 MPCB_FM_FN void fm_sincos(double x, double* s, double* c) {
-  if (!(fabs(x) < 1.0e5)) {  // huge / NaN / Inf: library path (never taken by sane headings)
+  if (!(fabs(x) < 131072.0)) {  // huge / NaN / Inf: library path (never taken by sane headings)
     *s = sin(x);
     *c = cos(x);
     return;
@@ -70,6 +114,23 @@ MPCB_FM_FN void fm_sincos(double x, double* s, double* c) {
   *c = ((q + 1) & 2) ? -cc : cc;
 }
 
+// sin(x) alone (value-only evaluations skip the cosine kernel unless the quadrant asks for it).
+MPCB_FM_FN double fm_sin(double x) {
+  if (!(fabs(x) < 131072.0)) return sin(x);
+  const double magic = 6755399441055744.0;
+  double kd = fma(x, MPCB_FM_TWO_OVER_PI, magic);
+  int q = fm_lo32(kd);
+  double k = kd - magic;
+  double r = fma(-k, MPCB_FM_PIO2_1, x);
+  r = fma(-k, MPCB_FM_PIO2_2, r);
+  r = fma(-k, MPCB_FM_PIO2_3, r);
+  double z = r * r;
+  double v;
+  if (q & 1) v = fma(z * z, fm_poly_cos(z), fma(-0.5, z, 1.0));
+  else v = fma(r * z, fm_poly_sin(z), r);
+  return (q & 2) ? -v : v;
+}
+
 // atan(x), all finite x (and +-Inf -> +-pi/2, NaN -> NaN).
 MPCB_FM_FN double fm_atan(double x) {
   double ax = fabs(x);
@@ -80,7 +141,7 @@ MPCB_FM_FN double fm_atan(double x) {
   } else {
     bool big = ax > 1.0;
     double t = ax;
-    if (big) t = (ax < 1.0e300) ? fm_rcp(ax) : 0.0;
+    if (big) t = (ax < 0x1p1000) ? fm_rcp(ax) : 0.0;
     double z = t * t;
     r = fma(t * z, fm_poly_atan_full(z), t);
     if (big) r = (MPCB_FM_PIO2_1 - r) + MPCB_FM_PIO2_2;

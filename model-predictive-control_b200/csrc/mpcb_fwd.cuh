@@ -1,0 +1,323 @@
+// mpcb_fwd.cuh — psi / grad psi of one MPC instance on one lane, forward ("tangent") mode.
+//
+// What it replaces: the CasADi-generated `f` / `grad_f` (reference main.py:54) over the RK4
+// single-shooting rollout (car_dynamics.py:134-166) and the stage cost (car_dynamics.py:230-258).
+//
+// Why forward mode.  The gradient CasADi produces is the reverse sweep through 16 N model calls.  On
+// the GPU that costs a second pass that re-evaluates every transcendental (or 48 KB of stored
+// linearisations per instance).  The stage map s_{n+1} = Psi(s_n, u_n) has only 5 non-trivial input
+// directions (vx, vy, omega, d, delta for Pacejka-6; v, d, delta for Kinematic-4):
+//   * d Psi / d(x, y) is the identity (the model never reads the position), and
+//   * d Psi / d phi follows from rotational equivariance, which RK4 preserves exactly (it commutes
+//     with affine maps):  d Psi/d phi = (-(y+ - y), x+ - x, 1, 0, ...).
+// So each model call propagates 5 (3) tangent vectors next to the primal and shares every
+// transcendental with it: +45 % fp64 instructions instead of +200 %, no checkpoints.  The horizon
+// adjoint is then a 20-step recursion over the stored stage Jacobians T_n (NX x ND doubles/stage):
+//   grad_n = T_n[:, u]^T lam + dL/du_n,   lam <- Phi_n^T lam + dL/ds.
+// Transcendentals are the short polynomial kernels of mpcb_fastmath.cuh.
+#pragma once
+#include <type_traits>
+#include "mpcb_eval.cuh"
+#include "mpcb_fastmath.cuh"
+
+namespace mpcb {
+
+template <int MODEL> struct Fm;
+
+// ---- Pacejka-6 (car_dynamics.py:93-129): q = (phi, vx, vy, omega) ------------------------------
+template <> struct Fm<MPCB_MODEL_PACEJKA6> {
+  static constexpr int NX = 6, NQ = 4, ND = 5;  // directions: vx, vy, omega, d, delta
+  struct Lin {
+    double s, c, f0, f1;
+    double a11, a12, a13, a21, a22, a23, a31, a32, a33;
+    double bd, bl1, bl2, bl3;
+  };
+  template <bool GRAD>
+  static MPCB_DEV void call(const double* q, const StageU& su, const VehP& v, double* kp, double* kq, Lin& L) {
+    const double vx = q[1], vy = q[2], w = q[3];
+    double s, c;
+    fm_sincos(q[0], &s, &c);
+    const double a_f = fma(w, v.lf, vy), a_r = fma(w, v.lr, -vy);
+    double thf, ar;
+    if (vx > 0x1p-960 && vx < 0x1p960) {  // atan2(a, vx) = atan(a / vx) for vx > 0
+      double r = fm_rcp(vx);
+      thf = fm_atan(a_f * r);
+      ar = fm_atan(a_r * r);
+    } else {  // reversing / standstill / non-finite: library path
+      thf = atan2(a_f, vx);
+      ar = atan2(a_r, vx);
+    }
+    const double af = su.dl - thf;
+    const double sgn = vx > 0.0 ? 1.0 : (vx < 0.0 ? -1.0 : 0.0);
+    const double frx = (v.cm1 - v.cm2 * vx) * su.d - v.cr0 * sgn - v.cr2 * vx * vx;
+    const double zf = v.bf * af, zr = v.br * ar;
+    double stf, ctf, str_, ctr;
+    if (GRAD) {
+      fm_sincos(v.cf * fm_atan(zf), &stf, &ctf);
+      fm_sincos(v.cr * fm_atan(zr), &str_, &ctr);
+    } else {
+      stf = fm_sin(v.cf * fm_atan(zf));
+      str_ = fm_sin(v.cr * fm_atan(zr));
+    }
+    const double ffy = v.df * stf, fry = v.dr * str_;
+    kp[0] = vx * c - vy * s;
+    kp[1] = vx * s + vy * c;
+    kq[0] = w;
+    kq[1] = (frx - ffy * su.sdl + v.m * vy * w) * v.inv_m;
+    kq[2] = (fry + ffy * su.cdl - v.m * vx * w) * v.inv_m;
+    kq[3] = (ffy * v.lf * su.cdl - fry * v.lr) * v.inv_iz;
+    if (GRAD) {
+      L.s = s; L.c = c; L.f0 = kp[0]; L.f1 = kp[1];
+      const double Gf = v.df * ctf * v.cf * v.bf * fm_rcp(fma(zf, zf, 1.0));
+      const double Gr = v.dr * ctr * v.cr * v.br * fm_rcp(fma(zr, zr, 1.0));
+      const double vx2 = vx * vx;
+      const double idf = fm_rcp(fma(a_f, a_f, vx2)), idr = fm_rcp(fma(a_r, a_r, vx2));
+      // P*1 = G * d(atan2)/dvx (sign folded below), P*2 = G * d(atan2)/da
+      const double Pf1 = Gf * a_f * idf, Pf2 = Gf * vx * idf;
+      const double Pr1 = Gr * a_r * idr, Pr2 = Gr * vx * idr;
+      const double sm = su.sdl * v.inv_m, cm = su.cdl * v.inv_m, lc = v.lf * su.cdl * v.inv_iz, lri = v.lr * v.inv_iz;
+      // d ffy = Pf1 dvx - Pf2 dvy - Pf2 lf dw + Gf ddelta ;  d fry = -Pr1 dvx - Pr2 dvy + Pr2 lr dw
+      L.a11 = (-v.cm2 * su.d - 2.0 * v.cr2 * vx) * v.inv_m - sm * Pf1;
+      L.a12 = sm * Pf2 + w;
+      L.a13 = sm * Pf2 * v.lf + vy;
+      L.a21 = -Pr1 * v.inv_m + cm * Pf1 - w;
+      L.a22 = -Pr2 * v.inv_m - cm * Pf2;
+      L.a23 = Pr2 * v.lr * v.inv_m - cm * Pf2 * v.lf - vx;
+      L.a31 = lc * Pf1 + lri * Pr1;
+      L.a32 = -lc * Pf2 + lri * Pr2;
+      L.a33 = -lc * Pf2 * v.lf - lri * Pr2 * v.lr;
+      L.bd = (v.cm1 - v.cm2 * vx) * v.inv_m;
+      const double gl = Gf * su.cdl - ffy * su.sdl;
+      L.bl1 = -(Gf * su.sdl + ffy * su.cdl) * v.inv_m;
+      L.bl2 = gl * v.inv_m;
+      L.bl3 = gl * v.lf * v.inv_iz;
+    }
+  }
+  // tangent of one direction J at the same stage point: tq = (phi', vx', vy', w')
+  template <int J>
+  static MPCB_DEV void tan(const Lin& L, const double* tq, double* tkp, double* tkq) {
+    tkp[0] = fma(L.c, tq[1], fma(-L.s, tq[2], -L.f1 * tq[0]));
+    tkp[1] = fma(L.s, tq[1], fma(L.c, tq[2], L.f0 * tq[0]));
+    tkq[0] = tq[3];
+    double k1 = fma(L.a11, tq[1], fma(L.a12, tq[2], L.a13 * tq[3]));
+    double k2 = fma(L.a21, tq[1], fma(L.a22, tq[2], L.a23 * tq[3]));
+    double k3 = fma(L.a31, tq[1], fma(L.a32, tq[2], L.a33 * tq[3]));
+    if (J == 3) k1 += L.bd;
+    if (J == 4) { k1 += L.bl1; k2 += L.bl2; k3 += L.bl3; }
+    tkq[1] = k1; tkq[2] = k2; tkq[3] = k3;
+  }
+  // unit seed of direction J at the stage start
+  template <int J>
+  static MPCB_DEV void seed(double* tq) {
+    tq[0] = 0.0; tq[1] = J == 0 ? 1.0 : 0.0; tq[2] = J == 1 ? 1.0 : 0.0; tq[3] = J == 2 ? 1.0 : 0.0;
+  }
+};
+
+// ---- Kinematic-4 (dynamics.py:144-173): q = (phi, v), directions v, d, delta ---------------------
+template <> struct Fm<MPCB_MODEL_KINEMATIC4> {
+  static constexpr int NX = 4, NQ = 2, ND = 3;
+  struct Lin { double s, c, v, sb_lr, cb_lr_db, db, acc, mu; };
+  template <bool GRAD>
+  static MPCB_DEV void call(const double* q, const StageU& su, const VehP& v, double* kp, double* kq, Lin& L) {
+    double s, c;
+    fm_sincos(q[0] + su.beta, &s, &c);
+    kp[0] = q[1] * c;
+    kp[1] = q[1] * s;
+    kq[0] = q[1] * su.sb * v.inv_lr;
+    kq[1] = v.acc * su.d - v.mu * q[1];
+    if (GRAD) {
+      L.s = s; L.c = c; L.v = q[1]; L.sb_lr = su.sb * v.inv_lr; L.cb_lr_db = su.cb * v.inv_lr * su.dbeta;
+      L.db = su.dbeta; L.acc = v.acc; L.mu = v.mu;
+    }
+  }
+  template <int J>
+  static MPCB_DEV void tan(const Lin& L, const double* tq, double* tkp, double* tkq) {
+    double ta = tq[0];
+    if (J == 2) ta += L.db;  // beta' = dbeta/ddelta
+    tkp[0] = fma(L.c, tq[1], -L.v * L.s * ta);
+    tkp[1] = fma(L.s, tq[1], L.v * L.c * ta);
+    double k0 = tq[1] * L.sb_lr;
+    if (J == 2) k0 = fma(L.v, L.cb_lr_db, k0);
+    double k1 = -L.mu * tq[1];
+    if (J == 1) k1 += L.acc;
+    tkq[0] = k0; tkq[1] = k1;
+  }
+  template <int J>
+  static MPCB_DEV void seed(double* tq) { tq[0] = 0.0; tq[1] = J == 0 ? 1.0 : 0.0; }
+};
+
+// Compile-time loop over tangent directions (J must be a constant inside Fm::tan / Fm::seed).
+template <int J, int ND> struct ForDir {
+  template <class F> static MPCB_DEV void run(F&& f) {
+    f(std::integral_constant<int, J>{});
+    ForDir<J + 1, ND>::run(f);
+  }
+};
+template <int ND> struct ForDir<ND, ND> {
+  template <class F> static MPCB_DEV void run(F&&) {}
+};
+
+// One RK4 element (car_dynamics.py:134-147) on p = (x, y), q = (phi, velocities), with tangents
+// tp[j] = (x', y'), tq[j] = q' of every direction j.  Position tangents never feed back, so they are
+// accumulated in place.
+template <int MODEL, bool GRAD>
+MPCB_DEV void rk4_fm(double* p, double* q, double (*tp)[2], double (*tq)[Fm<MODEL>::NQ], const StageU& su,
+                     const VehP& v, double h) {
+  using M = Fm<MODEL>;
+  constexpr int NQ = M::NQ, ND = M::ND;
+  const double hh = 0.5 * h, h6 = h * (1.0 / 6.0), h3 = h * (1.0 / 3.0);
+  double kp[2], kq[NQ], accp[2], accq[NQ], sq[NQ];
+  double taq[GRAD ? ND : 1][NQ], tsq[GRAD ? ND : 1][NQ];
+  typename M::Lin L;
+  // stage 1
+  M::template call<GRAD>(q, su, v, kp, kq, L);
+  accp[0] = kp[0]; accp[1] = kp[1];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) { accq[i] = kq[i]; sq[i] = fma(hh, kq[i], q[i]); }
+  if (GRAD) {
+    ForDir<0, ND>::run([&](auto J) {
+      constexpr int j = decltype(J)::value;
+      double tkp[2], tkq[NQ];
+      M::template tan<j>(L, tq[j], tkp, tkq);
+      tp[j][0] = fma(h6, tkp[0], tp[j][0]); tp[j][1] = fma(h6, tkp[1], tp[j][1]);
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) { taq[j][i] = tkq[i]; tsq[j][i] = fma(hh, tkq[i], tq[j][i]); }
+    });
+  }
+  // stage 2
+  M::template call<GRAD>(sq, su, v, kp, kq, L);
+  accp[0] = fma(2.0, kp[0], accp[0]); accp[1] = fma(2.0, kp[1], accp[1]);
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) { accq[i] = fma(2.0, kq[i], accq[i]); sq[i] = fma(hh, kq[i], q[i]); }
+  if (GRAD) {
+    ForDir<0, ND>::run([&](auto J) {
+      constexpr int j = decltype(J)::value;
+      double tkp[2], tkq[NQ];
+      M::template tan<j>(L, tsq[j], tkp, tkq);
+      tp[j][0] = fma(h3, tkp[0], tp[j][0]); tp[j][1] = fma(h3, tkp[1], tp[j][1]);
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) { taq[j][i] = fma(2.0, tkq[i], taq[j][i]); tsq[j][i] = fma(hh, tkq[i], tq[j][i]); }
+    });
+  }
+  // stage 3
+  M::template call<GRAD>(sq, su, v, kp, kq, L);
+  accp[0] = fma(2.0, kp[0], accp[0]); accp[1] = fma(2.0, kp[1], accp[1]);
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) { accq[i] = fma(2.0, kq[i], accq[i]); sq[i] = fma(h, kq[i], q[i]); }
+  if (GRAD) {
+    ForDir<0, ND>::run([&](auto J) {
+      constexpr int j = decltype(J)::value;
+      double tkp[2], tkq[NQ];
+      M::template tan<j>(L, tsq[j], tkp, tkq);
+      tp[j][0] = fma(h3, tkp[0], tp[j][0]); tp[j][1] = fma(h3, tkp[1], tp[j][1]);
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) { taq[j][i] = fma(2.0, tkq[i], taq[j][i]); tsq[j][i] = fma(h, tkq[i], tq[j][i]); }
+    });
+  }
+  // stage 4
+  M::template call<GRAD>(sq, su, v, kp, kq, L);
+  p[0] = fma(h6, accp[0] + kp[0], p[0]);
+  p[1] = fma(h6, accp[1] + kp[1], p[1]);
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) q[i] = fma(h6, accq[i] + kq[i], q[i]);
+  if (GRAD) {
+    ForDir<0, ND>::run([&](auto J) {
+      constexpr int j = decltype(J)::value;
+      double tkp[2], tkq[NQ];
+      M::template tan<j>(L, tsq[j], tkp, tkq);
+      tp[j][0] = fma(h6, tkp[0], tp[j][0]); tp[j][1] = fma(h6, tkp[1], tp[j][1]);
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) tq[j][i] = fma(h6, taq[j][i] + tkq[i], tq[j][i]);
+    });
+  }
+}
+
+// Doubles of scratch one gradient evaluation needs per lane: per stage T (NX x ND), dx, dy, dL/ds (NX).
+template <int MODEL>
+__host__ __device__ constexpr int fm_stage_doubles() { return Fm<MODEL>::NX * Fm<MODEL>::ND + 2 + Fm<MODEL>::NX; }
+
+// psi (returned) and, with GRAD and store, grad psi into `grad`.  states/idx_out (p may be null)
+// receive the stage-end states and nearest-vertex indices.
+template <int MODEL, bool GRAD>
+MPCB_DEV double eval_fm(const KDesc& d, const VehP& v, const RoadView& r, const Extras& ex, const double* x0,
+                        const Vec& U, const Vec& scr, const Vec& grad, bool store, const Vec& states = Vec{nullptr, 0},
+                        const IVec& idx_out = IVec{nullptr, 0}) {
+  using M = Fm<MODEL>;
+  constexpr int NX = M::NX, NQ = M::NQ, ND = M::ND, K = fm_stage_doubles<MODEL>();
+  double p[2] = {x0[0], x0[1]}, q[NQ];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) q[i] = x0[2 + i];
+  double cost = 0.0;
+#pragma unroll 1
+  for (int n = 0; n < d.N; ++n) {
+    const double ud = U(2 * n), udl = U(2 * n + 1);
+    StageU su;
+    make_stage_u<MODEL>(su, ud, udl, v, GRAD);
+    double tp[GRAD ? ND : 1][2], tq[GRAD ? ND : 1][NQ];
+    if (GRAD) {
+      ForDir<0, ND>::run([&](auto J) {
+        constexpr int j = decltype(J)::value;
+        tp[j][0] = 0.0; tp[j][1] = 0.0;
+        M::template seed<j>(tq[j]);
+      });
+    }
+    const double px0 = p[0], py0 = p[1];
+#pragma unroll 1
+    for (int e = 0; e < d.n_sub; ++e) rk4_fm<MODEL, GRAD>(p, q, tp, tq, su, v, d.h);
+    double y[NX], gy[NX], gu[2];
+    y[0] = p[0]; y[1] = p[1];
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) y[2 + i] = q[i];
+    int idx;
+    cost += stage_cost<MODEL, GRAD, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
+    if (states.p) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) states.set(n * NX + i, y[i]);
+    }
+    if (idx_out.p) idx_out.set(n, idx);
+    if (GRAD && store) {
+      const int o = n * K;
+#pragma unroll
+      for (int j = 0; j < ND; ++j) {
+        scr.set(o + j * NX, tp[j][0]);
+        scr.set(o + j * NX + 1, tp[j][1]);
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) scr.set(o + j * NX + 2 + i, tq[j][i]);
+      }
+      scr.set(o + NX * ND, p[0] - px0);
+      scr.set(o + NX * ND + 1, p[1] - py0);
+#pragma unroll
+      for (int i = 0; i < NX; ++i) scr.set(o + NX * ND + 2 + i, gy[i]);
+    }
+  }
+  if (GRAD && store) {
+    // horizon adjoint over the stored stage Jacobians
+    double lam[NX];
+#pragma unroll
+    for (int i = 0; i < NX; ++i) lam[i] = 0.0;
+#pragma unroll 1
+    for (int n = d.N - 1; n >= 0; --n) {
+      const int o = n * K;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) lam[i] += scr(o + NX * ND + 2 + i);
+      double dots[ND];
+#pragma unroll
+      for (int j = 0; j < ND; ++j) {
+        double s = 0.0;
+#pragma unroll
+        for (int i = 0; i < NX; ++i) s = fma(scr(o + j * NX + i), lam[i], s);
+        dots[j] = s;
+      }
+      const double dx = scr(o + NX * ND), dy = scr(o + NX * ND + 1);
+      const double ud = U(2 * n), udl = U(2 * n + 1);
+      grad.set(2 * n, fma(2.0 * d.c[5], ud, dots[ND - 2]));
+      grad.set(2 * n + 1, fma(2.0 * d.c[4], udl, dots[ND - 1]));
+      lam[2] = lam[2] - dy * lam[0] + dx * lam[1];
+#pragma unroll
+      for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
+    }
+  }
+  return cost;
+}
+
+}  // namespace mpcb

@@ -1,6 +1,6 @@
 // mpcb_kernels.cuh — utility, rollout and value+gradient kernels (instance-per-lane).
 #pragma once
-#include "mpcb_eval.cuh"
+#include "mpcb_fwd.cuh"
 
 namespace mpcb {
 
@@ -39,15 +39,15 @@ __global__ void k_plant_step(KDesc d, int64_t B, const double* __restrict__ x, c
   __syncthreads();
   int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
-  double y[NX];
+  double pq[NX];
 #pragma unroll
-  for (int i = 0; i < NX; ++i) y[i] = x[b * NX + i];
+  for (int i = 0; i < NX; ++i) pq[i] = x[b * NX + i];
   StageU su;
   make_stage_u<MODEL>(su, u[2 * b], u[2 * b + 1], v, false);
 #pragma unroll 1
-  for (int e = 0; e < d.n_sub; ++e) rk4_element<MODEL>(y, su, v, d.h);
+  for (int e = 0; e < d.n_sub; ++e) rk4_fm<MODEL, false>(pq, pq + 2, nullptr, nullptr, su, v, d.h);
 #pragma unroll
-  for (int i = 0; i < NX; ++i) out[b * NX + i] = y[i];
+  for (int i = 0; i < NX; ++i) out[b * NX + i] = pq[i];
 }
 
 // ---- car_dynamics.py:194-228 / road.py:52-81 as a batched query ---------------------------------
@@ -145,36 +145,23 @@ k_rollout(KDesc d, int64_t B, const double* __restrict__ x0, const double* __res
   Extras ex{obs ? obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, nullptr, nullptr, 0, 0};
   Vec Uv{const_cast<double*>(U) + b * d.n, 1};
   // stage-end states and nearest indices go straight to the caller's row-major outputs
-  double y[NX];
+  double y0[NX];
 #pragma unroll
-  for (int i = 0; i < NX; ++i) y[i] = x0[b * NX + i];
-  double cost = 0.0;
-#pragma unroll 1
-  for (int n = 0; n < d.N; ++n) {
-    double ud = Uv(2 * n), udl = Uv(2 * n + 1);
-    StageU su;
-    make_stage_u<MODEL>(su, ud, udl, v, false);
-#pragma unroll 1
-    for (int e = 0; e < d.n_sub; ++e) rk4_element<MODEL>(y, su, v, d.h);
-    int idx;
-    cost += stage_cost<MODEL, false, true>(d, r, ex, n, y, ud, udl, &idx, nullptr, nullptr);
-    if (states_out) {
-#pragma unroll
-      for (int i = 0; i < NX; ++i) states_out[(b * d.N + n) * NX + i] = y[i];
-    }
-    if (idx_out) idx_out[b * d.N + n] = idx;
-  }
+  for (int i = 0; i < NX; ++i) y0[i] = x0[b * NX + i];
+  double cost = eval_fm<MODEL, false>(d, v, r, ex, y0, Uv, Vec{nullptr, 0}, Vec{nullptr, 0}, false,
+                                      Vec{states_out ? states_out + b * d.N * NX : nullptr, 1},
+                                      IVec{idx_out ? idx_out + b * d.N : nullptr, 1});
   if (cost_out) cost_out[b] = cost;
 }
 
-// ---- psi + grad psi: forward with checkpoints, reverse sweep --------------------------------------
-// Persistent grid-stride over instances; scratch is lane-interleaved by global thread id (slot).
+// ---- psi + grad psi: forward-mode rollout + horizon adjoint (mpcb_fwd.cuh) --------------------------
+// Persistent grid-stride over instances; the stage-Jacobian scratch is lane-interleaved by slot.
 template <int MODEL>
 __global__ void __launch_bounds__(128)
 k_value_grad(KDesc d, int64_t B, const double* __restrict__ x0, const double* __restrict__ U,
              const double* __restrict__ p, RoadArg ra, const double* __restrict__ obs,
              const double* __restrict__ lam, const double* __restrict__ Sig, double* __restrict__ cost_out,
-             double* __restrict__ grad_out, double* scratch, int32_t* iscratch, int64_t ns) {
+             double* __restrict__ grad_out, double* scratch, int64_t ns) {
   constexpr int NX = ModelTraits<MODEL>::NX;
   extern __shared__ double sroad[];
   __shared__ VehP v;
@@ -182,10 +169,7 @@ k_value_grad(KDesc d, int64_t B, const double* __restrict__ x0, const double* __
   if (ra.in_smem) stage_roads(sroad, ra.road, ra.R, d.S);
   __syncthreads();
   int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  EvalScratch sc;
-  sc.chk = Vec{scratch + slot, ns};
-  sc.st = Vec{scratch + (int64_t)d.N * d.n_sub * NX * ns + slot, ns};
-  sc.idx = IVec{iscratch + slot, ns};
+  const Vec scr{scratch + slot, ns};
   for (int64_t b = slot; b < B; b += ns) {
     RoadView r = road_view(ra, sroad, d.S, b);
     Extras ex{obs ? obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, lam ? lam + b * d.m : nullptr,
@@ -195,9 +179,7 @@ k_value_grad(KDesc d, int64_t B, const double* __restrict__ x0, const double* __
     for (int i = 0; i < NX; ++i) y0[i] = x0[b * NX + i];
     Vec Uv{const_cast<double*>(U) + b * d.n, 1};
     Vec Gv{grad_out + b * d.n, 1};
-    double cost = eval_forward<MODEL>(d, v, r, ex, y0, Uv, sc, true);
-    eval_reverse<MODEL>(d, v, r, ex, Uv, sc, Gv);
-    cost_out[b] = cost;
+    cost_out[b] = eval_fm<MODEL, true>(d, v, r, ex, y0, Uv, scr, Gv, true);
   }
 }
 

@@ -13,7 +13,7 @@
 // accesses to element i of 32 instances are one 256-byte coalesced transaction.
 #pragma once
 #include <float.h>
-#include "mpcb_eval.cuh"
+#include "mpcb_fwd.cuh"
 
 namespace mpcb {
 
@@ -42,7 +42,7 @@ struct WsMap {
   __host__ __device__ WsMap(int n_, int mem_, int N, int n_sub, int nx, int m) : n(n_), mem(mem_) {
     Q = 8 * n; XE = 9 * n; GE = 10 * n; XB = 11 * n;
     LS = 12 * n; LY = LS + mem * n; AL = LY + mem * n; RH = AL + mem;
-    CHK = RH + mem; ST = CHK + N * n_sub * nx; SIG = ST + N * nx; E1 = SIG + m; E2 = E1 + m; total = E2 + m;
+    CHK = RH + mem; ST = CHK + N * (nx * (nx - 1) + 2 + nx); SIG = ST + N * nx; E1 = SIG + m; E2 = E1 + m; total = E2 + m;
   }
   __host__ __device__ int X(int bank) const { return bank * 4 * n; }
   __host__ __device__ int G(int bank) const { return bank * 4 * n + n; }
@@ -70,10 +70,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const WsMap M(n, mem, d.N, d.n_sub, NX, m);
   auto W = [&](int row) { return Vec{a.ws + (int64_t)row * ns + slot, ns}; };
-  EvalScratch sc;
-  sc.chk = W(M.CHK);
-  sc.st = W(M.ST);
-  sc.idx = IVec{a.wsi + slot, ns};
+  const Vec scr = W(M.CHK);  // stage Jacobians of the forward-mode evaluation
 
   // ---- per-lane registers ----
   int state = ST_IDLE, want = 0, ep = 0, eg = 0;
@@ -404,13 +401,11 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
 #pragma unroll
       for (int i = 0; i < NX; ++i) y0[i] = a.x0[b * NX + i];
       Vec Uv = W(ep);
-      val = eval_forward<MODEL>(d, v, r, ex, y0, Uv, sc, want >= 2);
-      if (want == 2) {
-        eval_reverse<MODEL>(d, v, r, ex, Uv, sc, W(eg));
-        ++n_grad;
-      } else if (want == 1) {
-        ++n_val;
-      }
+      const Vec stv = want == 3 ? W(M.ST) : Vec{nullptr, 0};
+      if (__any_sync(__activemask(), want == 2)) val = eval_fm<MODEL, true>(d, v, r, ex, y0, Uv, scr, W(eg), want == 2, stv);
+      else val = eval_fm<MODEL, false>(d, v, r, ex, y0, Uv, scr, W(eg), false, stv);
+      if (want == 2) ++n_grad;
+      else if (want == 1) ++n_val;
     }
   }
 }

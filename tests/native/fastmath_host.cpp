@@ -6,6 +6,9 @@ extern "C" {
 void fmh_sincos(const double* x, double* s, double* c, long n) {
   for (long i = 0; i < n; ++i) mpcb::fm_sincos(x[i], &s[i], &c[i]);
 }
+void fmh_sin(const double* x, double* y, long n) {
+  for (long i = 0; i < n; ++i) y[i] = mpcb::fm_sin(x[i]);
+}
 void fmh_atan(const double* x, double* y, long n) {
   for (long i = 0; i < n; ++i) y[i] = mpcb::fm_atan(x[i]);
 }

@@ -24,6 +24,7 @@ def fm():
     dp = C.POINTER(C.c_double)
     lib.fmh_sincos.argtypes = [dp, dp, dp, C.c_long]
     lib.fmh_atan.argtypes = [dp, dp, C.c_long]
+    lib.fmh_sin.argtypes = [dp, dp, C.c_long]
     return lib
 
 
@@ -47,6 +48,9 @@ def test_sincos_matches_libm(fm):
     big = np.abs(np.sin(x)) > 0.1
     assert _ulps(s[big], np.sin(x[big])).max() <= 2.0
     assert np.all(s * s + c * c - 1.0 < 1e-15)
+    s1 = np.empty_like(x)
+    fm.fmh_sin(_ptr(x), _ptr(s1), x.size)
+    assert np.array_equal(s1, s)  # fm_sin is the sine half of fm_sincos, bit for bit
     n = np.array([np.nan, np.inf])
     fm.fmh_sincos(_ptr(n), _ptr(s), _ptr(c), 2)
     assert np.isnan(s[:2]).all() and np.isnan(c[:2]).all()
