@@ -3,6 +3,7 @@
 // every entry point fails with MPCB_E_NODEVICE / MPCB_E_CUDA when the GPU path cannot run.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -22,7 +23,9 @@ struct MpcHandle {
   // grow-only device scratch
   double* road_t = nullptr; size_t road_t_cap = 0;     // transposed per-instance roads [2S, ld]
   double* ws = nullptr; size_t ws_cap = 0;             // solver / value_grad workspace
-  int32_t* wsi = nullptr; size_t wsi_cap = 0;
+  double* wst = nullptr; size_t wst_cap = 0;           // per-tile solver workspace
+  int tile_override = 0;                               // MPCB_TILE env: force the lanes-per-instance width
+  int last_tile = 0;
   unsigned long long* queue = nullptr;
   double* zero_lam = nullptr; size_t zero_lam_cap = 0;
   // staging for *_host entry points
@@ -191,13 +194,17 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
   if (cudaMalloc((void**)&h->queue, sizeof(unsigned long long)) != cudaSuccess) { delete h; return MPCB_E_CUDA; }
   if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
   if (cudaEventCreateWithFlags(&h->last_ev, cudaEventDisableTiming) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
+  if (const char* e = std::getenv("MPCB_TILE")) {
+    int g = std::atoi(e);
+    if (g == 1 || g == 2 || g == 4 || g == 8) h->tile_override = g;
+  }
   *out = h;
   return MPCB_OK;
 }
 
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
-  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wsi); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
+  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
   if (h->pin) cudaFreeHost(h->pin);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   if (h->last_ev) cudaEventDestroy(h->last_ev);
@@ -336,26 +343,47 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   RoadArg ra; size_t smem;
   if ((rc = prepare_road(h, B, road, road_idx, st, &ra, &smem))) return rc;
   smem += (size_t)2 * k.n * sizeof(double);
-  const int block = 128;
-  int64_t max_blocks = (int64_t)h->num_sms * 2;  // 255-register lanes: 2 CTAs of 128 per SM
-  int64_t blocks = (B + block - 1) / block;
+  // Tile width: the solve is latency-bound, so spare lanes are spent on speculative line-search
+  // candidates (mpcb_solve.cuh).  255-register lanes: 8 warps per SM resident.
+  const int block = 64;
+  const int64_t lane_cap = (int64_t)h->num_sms * 8 * 32;
+  int G = 1;
+  for (int g : {8, 4, 2}) if (B * g <= lane_cap) { G = g; break; }
+  if (h->tile_override > 0) G = h->tile_override;
+  int64_t tiles_wanted = B;
+  int64_t blocks = (tiles_wanted * G + block - 1) / block;
+  const int64_t max_blocks = lane_cap / block;
   if (blocks > max_blocks) blocks = max_blocks;
-  int64_t ns = blocks * block;
-  WsMap M(k.n, sp->lbfgs_mem, k.N, k.n_sub, k.nx, k.m);
-  if ((rc = grow(h, &h->ws, &h->ws_cap, (size_t)M.total * ns * sizeof(double), st))) return rc;
-  if ((rc = grow(h, &h->wsi, &h->wsi_cap, (size_t)k.N * ns * sizeof(int32_t), st))) return rc;
+  const int64_t ns = blocks * block, nt = ns / G;
+  const bool bounded = k.bounded != 0;
+  const int stage_doubles = k.model_id == MPCB_MODEL_PACEJKA6 ? fm_stage_doubles<MPCB_MODEL_PACEJKA6>()
+                                                              : fm_stage_doubles<MPCB_MODEL_KINEMATIC4>();
+  LaneMap LM(k.n, k.N, k.nx, stage_doubles, bounded);
+  TileMap TM(k.n, G, sp->lbfgs_mem, k.m, bounded);
+  if ((rc = grow(h, &h->ws, &h->ws_cap, (size_t)LM.total * ns * sizeof(double), st))) return rc;
+  if ((rc = grow(h, &h->wst, &h->wst_cap, (size_t)TM.total * nt * sizeof(double), st))) return rc;
   CK(cudaMemsetAsync(h->queue, 0, sizeof(unsigned long long), st));
   SolveArgs a;
   a.B = B; a.x0 = x0; a.p = p; a.obs = obs; a.lb = lb; a.ub = ub; a.ra = ra; a.U = U; a.lam = lambda;
   a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res;
-  a.ws = h->ws; a.wsi = h->wsi; a.ns = ns; a.queue = h->queue;
-  if (k.model_id == MPCB_MODEL_PACEJKA6) {
-    if ((rc = set_smem(h, k_solve<MPCB_MODEL_PACEJKA6>, smem))) return rc;
-    k_solve<MPCB_MODEL_PACEJKA6><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);
-  } else {
-    if ((rc = set_smem(h, k_solve<MPCB_MODEL_KINEMATIC4>, smem))) return rc;
-    k_solve<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);
+  a.ws = h->ws; a.wst = h->wst; a.ns = ns; a.nt = nt; a.queue = h->queue;
+#define MPCB_LAUNCH_SOLVE(MODEL, GG)                                                           \
+  do {                                                                                         \
+    if ((rc = set_smem(h, k_solve<MODEL, GG>, smem))) return rc;                               \
+    k_solve<MODEL, GG><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);                      \
+  } while (0)
+#define MPCB_LAUNCH_SOLVE_G(MODEL)                                                             \
+  switch (G) {                                                                                 \
+    case 8: MPCB_LAUNCH_SOLVE(MODEL, 8); break;                                                \
+    case 4: MPCB_LAUNCH_SOLVE(MODEL, 4); break;                                                \
+    case 2: MPCB_LAUNCH_SOLVE(MODEL, 2); break;                                                \
+    default: MPCB_LAUNCH_SOLVE(MODEL, 1); break;                                               \
   }
+  if (k.model_id == MPCB_MODEL_PACEJKA6) { MPCB_LAUNCH_SOLVE_G(MPCB_MODEL_PACEJKA6) }
+  else { MPCB_LAUNCH_SOLVE_G(MPCB_MODEL_KINEMATIC4) }
+#undef MPCB_LAUNCH_SOLVE_G
+#undef MPCB_LAUNCH_SOLVE
+  h->last_tile = G;
   h->launches++;
   return leave(h, st);
 }

@@ -30,6 +30,7 @@ struct KDesc {
 struct VehP {
   double lf, lr, m, iz, inv_m, inv_iz, cm1, cm2, cr0, cr2, bf, cf, df, br, cr, dr;
   double max_steer, max_drive, acc, mu, inv_lr, lflr;
+  int trig_ok;  // |cf|, |cr| small enough for the unguarded sincos reduction of cf*atan(.)
 };
 
 MPCB_DEV void load_vehicle(VehP* v, const double* __restrict__ p, const KDesc& d) {
@@ -39,11 +40,15 @@ MPCB_DEV void load_vehicle(VehP* v, const double* __restrict__ p, const KDesc& d
   v->bf = p[11]; v->cf = p[12]; v->df = p[13]; v->br = p[14]; v->cr = p[15]; v->dr = p[16];
   v->cm1 = p[17]; v->cm2 = p[18]; v->cr0 = p[19]; v->cr2 = p[21];
   v->acc = d.kin_acc; v->mu = d.kin_mu; v->inv_lr = 1.0 / p[2]; v->lflr = p[1] + p[2];
+  v->trig_ok = fabs(p[12]) < 8.0e4 && fabs(p[15]) < 8.0e4;
 }
 
 // Stage input with its hoisted trigonometry (delta is constant over the 16 model calls of a stage).
 struct StageU {
   double d, dl, sdl, cdl;
+  // Pacejka-6 fast path (mpcb_fwd.cuh): 2 = the second-stage atan arguments bf*af, br*ar are within 0.5
+  // whenever the slip tangents are, 1 = within 1 whenever the slip tangents are within 1, 0 = neither
+  int z2_mode;
   // Kinematic-4 only: beta = atan2(lf tan(dl), lf+lr) and its derivative wrt dl
   double beta, sb, cb, dbeta;
 };
@@ -53,6 +58,12 @@ MPCB_DEV void make_stage_u(StageU& su, double d, double dl, const VehP& v, bool 
   su.d = d; su.dl = dl;
   if constexpr (MODEL == MPCB_MODEL_PACEJKA6) {
     sincos(dl, &su.sdl, &su.cdl);
+    const double adl = fabs(dl), abf = fabs(v.bf), abr = fabs(v.br);
+    su.z2_mode = 0;
+    if (v.trig_ok) {
+      if (abf * (adl + 0.46365) <= 0.5 && abr * 0.46365 <= 0.5) su.z2_mode = 2;         // atan(0.5) = 0.46365
+      else if (abf * (adl + 0.78540) <= 1.0 && abr * 0.78540 <= 1.0) su.z2_mode = 1;    // atan(1) = pi/4
+    }
   } else {
     double tl = tan(dl);
     double num = v.lf * tl;

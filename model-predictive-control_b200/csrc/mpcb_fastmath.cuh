@@ -1,13 +1,18 @@
-// mpcb_fastmath.cuh — short, branch-light fp64 sincos / atan / reciprocal for the solver kernels.
+// mpcb_fastmath.cuh — short fp64 sincos / atan / reciprocal kernels for the solver kernels.
 //
-// Why: the solve is bound by the number of FP64-pipe instructions one model call issues (a lone warp
-// issues one DFMA per ~3.75 cycles on B200, profiles/r01_ubench.json).  libdevice's atan2/atan/sin
-// cost ~60-120 fp64 instructions each with slow-path branches; the versions below cost 18-27 and are
-// accurate to ~1 ulp (approximation error < 6e-18, tools/gen_fastmath.py), far inside the 1e-9
+// Why: one Pacejka model call is 4 atan + 3 sincos + a division, and the solve does 16 N of them in
+// a dependent chain per evaluation.  With libdevice (or any branchy implementation) the call is
+// latency-bound at ~2050 cycles for a lone warp: every transcendental is its own serial Horner chain
+// and the branches keep ptxas from interleaving the independent front/rear tyre chains
+// (profiles/r01_ubench_model_v2a.json).  The *_x2 kernels below are branch-free, evaluate two
+// arguments statement by statement (ILP 2, one materialised coefficient feeds two DFMAs), and split
+// every polynomial into even/odd halves (half the dependent depth).  Callers check the argument
+// ranges once per model call and fall back to the general (branchy) versions otherwise.
+// Accuracy ~1 ulp (approximation error < 2.3e-17, tools/gen_fastmath.py), far inside the 1e-9
 // rollout tolerance against the oracle's libm.
 //
-// The same header compiles as plain host C++ (tests/test_fastmath_cpu.py checks it against libm on
-// the CPU): fm_rcp falls back to 1/x there, everything else is identical arithmetic.
+// The same header compiles as plain host C++ (tests/test_fastmath_cpu.py checks every kernel against
+// libm on the CPU): fm_rcp falls back to 1/x there, everything else is identical arithmetic.
 #pragma once
 #include <math.h>
 #include <stdint.h>
@@ -20,31 +25,27 @@
 #endif
 
 // How device code gets polynomial coefficients (sm_100a DFMA takes register, uniform-register or
-// 32-bit-immediate operands only): 0 = literals (two UMOV each), 1 = __constant__ tables,
-// 2 = one shared-memory table filled by fm_load_smem() at kernel start.  Measured with
-// tools/ubench_model.cu; see profiles/r01_ubench_model.json.
+// 32-bit-immediate operands only, no constant-bank operand): MPCB_FM_MODE 0 = literals (two UMOV per
+// coefficient, shared by the paired evaluators), 2 = one shared-memory table filled by fm_load_smem()
+// at kernel start (one LDS.64 per coefficient).  Measured with tools/ubench_model.cu.
 #ifndef MPCB_FM_MODE
 #define MPCB_FM_MODE 0
 #endif
 #if defined(__CUDACC__)
-#define MPCB_FM_TABLE(name, n, ...)                  \
-  static const double name##_h[n] = {__VA_ARGS__};   \
-  static __constant__ double name##_d[n] = {__VA_ARGS__};
+#define MPCB_FM_TABLE(name, n, ...) static __constant__ double name##_d[n] = {__VA_ARGS__};
 #else
-#define MPCB_FM_TABLE(name, n, ...) static const double name##_h[n] = {__VA_ARGS__};
+#define MPCB_FM_TABLE(name, n, ...)
 #endif
-#if !defined(__CUDA_ARCH__)
-#define MPCB_FM_C(name) name##_h
-#elif MPCB_FM_MODE == 2
-#define MPCB_FM_C(name) (fm_smem + name##_off)
+#if defined(__CUDA_ARCH__) && MPCB_FM_MODE == 2
+#define MPCB_FM_K(name, i, lit) (fm_smem[name##_off + (i)])
 #else
-#define MPCB_FM_C(name) name##_d
+#define MPCB_FM_K(name, i, lit) (lit)
 #endif
 
 namespace mpcb {
 
 #if defined(__CUDACC__) && MPCB_FM_MODE == 2
-static __shared__ double fm_smem[64];
+static __shared__ double fm_smem[80];
 #endif
 
 #include "mpcb_fastmath_coef.h"
@@ -53,19 +54,14 @@ static __shared__ double fm_smem[64];
 // Mode 2: every kernel that uses the fm_* functions calls this once (all threads) before them.
 __device__ __forceinline__ void fm_load_smem() {
 #if MPCB_FM_MODE == 2
-  for (int i = threadIdx.x; i < MPCB_FM_SMEM_DOUBLES; i += blockDim.x) {
-    double v;
-    if (i < fm_c_atan_full_off) v = fm_c_atan_small_d[i];
-    else if (i < fm_c_sin_off) v = fm_c_atan_full_d[i - fm_c_atan_full_off];
-    else if (i < fm_c_cos_off) v = fm_c_sin_d[i - fm_c_sin_off];
-    else if (i < fm_c_misc_off) v = fm_c_cos_d[i - fm_c_cos_off];
-    else v = fm_c_misc_d[i - fm_c_misc_off];
-    fm_smem[i] = v;
-  }
+  for (int i = threadIdx.x; i < MPCB_FM_SMEM_DOUBLES; i += blockDim.x) fm_smem[i] = fm_c_all_d[i];
   __syncthreads();
 #endif
 }
 #endif
+
+#define MPCB_FM_MAGIC 6755399441055744.0 /* 1.5 * 2^52: adding it rounds to the nearest integer */
+#define MPCB_FM_TRIG_MAX 131072.0        /* Cody-Waite reduction below is exact enough for |x| < 2^17 */
 
 // 1/x to <= 1 ulp: MUFU seed (20 bits, measured 9.9e-7) + one third-order correction (3 DFMA).
 // Finite non-zero normal x only (callers guard).
@@ -91,17 +87,19 @@ MPCB_FM_FN int fm_lo32(double v) {
 #endif
 }
 
-// sin and cos of x.  Cody-Waite reduction with three FMA (valid for |x| < 2^17), 7-term kernels.
-MPCB_FM_FN void fm_sincos(double x, double* s, double* c) {
-  if (!(fabs(x) < 131072.0)) {  // huge / NaN / Inf: library path (never taken by sane headings)
-    *s = sin(x);
-    *c = cos(x);
-    return;
-  }
-  const double magic = 6755399441055744.0;  // 1.5 * 2^52: adding it rounds to nearest integer
-  double kd = fma(x, MPCB_FM_TWO_OVER_PI, magic);
+MPCB_FM_FN double fm_flip(double v, int neg) {  // neg != 0 -> -v (integer sign-bit flip, no fp64 slot)
+#if defined(__CUDA_ARCH__)
+  return __hiloint2double(__double2hiint(v) ^ (neg ? (int)0x80000000 : 0), __double2loint(v));
+#else
+  return neg ? -v : v;
+#endif
+}
+
+// ---- branch-free cores: the caller guarantees |x| < MPCB_FM_TRIG_MAX -------------------------------
+MPCB_FM_FN void fm_sincos_nr(double x, double* s, double* c) {
+  double kd = fma(x, MPCB_FM_TWO_OVER_PI, MPCB_FM_MAGIC);
   int q = fm_lo32(kd);
-  double k = kd - magic;
+  double k = kd - MPCB_FM_MAGIC;
   double r = fma(-k, MPCB_FM_PIO2_1, x);
   r = fma(-k, MPCB_FM_PIO2_2, r);
   r = fma(-k, MPCB_FM_PIO2_3, r);
@@ -110,25 +108,71 @@ MPCB_FM_FN void fm_sincos(double x, double* s, double* c) {
   double cr = fma(z * z, fm_poly_cos(z), fma(-0.5, z, 1.0));
   double ss = (q & 1) ? cr : sr;
   double cc = (q & 1) ? sr : cr;
-  *s = (q & 2) ? -ss : ss;
-  *c = ((q + 1) & 2) ? -cc : cc;
+  *s = fm_flip(ss, q & 2);
+  *c = fm_flip(cc, (q + 1) & 2);
 }
 
-// sin(x) alone (value-only evaluations skip the cosine kernel unless the quadrant asks for it).
+MPCB_FM_FN void fm_sincos_nr_x2(double x1, double x2, double* s1, double* c1, double* s2, double* c2) {
+  double kd1 = fma(x1, MPCB_FM_TWO_OVER_PI, MPCB_FM_MAGIC), kd2 = fma(x2, MPCB_FM_TWO_OVER_PI, MPCB_FM_MAGIC);
+  int q1 = fm_lo32(kd1), q2 = fm_lo32(kd2);
+  double k1 = kd1 - MPCB_FM_MAGIC, k2 = kd2 - MPCB_FM_MAGIC;
+  double r1 = fma(-k1, MPCB_FM_PIO2_1, x1), r2 = fma(-k2, MPCB_FM_PIO2_1, x2);
+  r1 = fma(-k1, MPCB_FM_PIO2_2, r1); r2 = fma(-k2, MPCB_FM_PIO2_2, r2);
+  r1 = fma(-k1, MPCB_FM_PIO2_3, r1); r2 = fma(-k2, MPCB_FM_PIO2_3, r2);
+  double z1 = r1 * r1, z2 = r2 * r2;
+  double ps1, ps2, pc1, pc2;
+  fm_poly_sin_x2(z1, z2, &ps1, &ps2);
+  fm_poly_cos_x2(z1, z2, &pc1, &pc2);
+  double sr1 = fma(r1 * z1, ps1, r1), sr2 = fma(r2 * z2, ps2, r2);
+  double cr1 = fma(z1 * z1, pc1, fma(-0.5, z1, 1.0)), cr2 = fma(z2 * z2, pc2, fma(-0.5, z2, 1.0));
+  double ss1 = (q1 & 1) ? cr1 : sr1, cc1 = (q1 & 1) ? sr1 : cr1;
+  double ss2 = (q2 & 1) ? cr2 : sr2, cc2 = (q2 & 1) ? sr2 : cr2;
+  *s1 = fm_flip(ss1, q1 & 2); *c1 = fm_flip(cc1, (q1 + 1) & 2);
+  *s2 = fm_flip(ss2, q2 & 2); *c2 = fm_flip(cc2, (q2 + 1) & 2);
+}
+
+// sin only, two arguments: reduction modulo pi and one odd kernel on [-pi/2, pi/2] (no cosine kernel,
+// no quadrant select) — what a value-only model call needs for the two Pacejka forces.
+MPCB_FM_FN void fm_sin_nr_x2(double x1, double x2, double* s1, double* s2) {
+  double kd1 = fma(x1, MPCB_FM_ONE_OVER_PI, MPCB_FM_MAGIC), kd2 = fma(x2, MPCB_FM_ONE_OVER_PI, MPCB_FM_MAGIC);
+  int q1 = fm_lo32(kd1), q2 = fm_lo32(kd2);
+  double k1 = kd1 - MPCB_FM_MAGIC, k2 = kd2 - MPCB_FM_MAGIC;
+  const double pi_hi = 2.0 * MPCB_FM_PIO2_1;
+  double r1 = fma(-k1, pi_hi, x1), r2 = fma(-k2, pi_hi, x2);
+  r1 = fma(-k1, MPCB_FM_PI_LO, r1); r2 = fma(-k2, MPCB_FM_PI_LO, r2);
+  double z1 = r1 * r1, z2 = r2 * r2;
+  double p1, p2;
+  fm_poly_sin_wide_x2(z1, z2, &p1, &p2);
+  *s1 = fm_flip(fma(r1 * z1, p1, r1), q1 & 1);
+  *s2 = fm_flip(fma(r2 * z2, p2, r2), q2 & 1);
+}
+
+// atan of two arguments with |x| <= 0.5 (SMALL) or |x| <= 1.
+template <bool SMALL>
+MPCB_FM_FN void fm_atan_nr_x2(double x1, double x2, double* y1, double* y2) {
+  double z1 = x1 * x1, z2 = x2 * x2;
+  double p1, p2;
+  if (SMALL) fm_poly_atan_small_x2(z1, z2, &p1, &p2);
+  else fm_poly_atan_full_x2(z1, z2, &p1, &p2);
+  *y1 = fma(x1 * z1, p1, x1);
+  *y2 = fma(x2 * z2, p2, x2);
+}
+
+// ---- general versions (any argument; branchy: slow path of the model call, utility kernels) -------
+MPCB_FM_FN void fm_sincos(double x, double* s, double* c) {
+  if (!(fabs(x) < MPCB_FM_TRIG_MAX)) {  // huge / NaN / Inf: library path
+    *s = sin(x);
+    *c = cos(x);
+    return;
+  }
+  fm_sincos_nr(x, s, c);
+}
+
 MPCB_FM_FN double fm_sin(double x) {
-  if (!(fabs(x) < 131072.0)) return sin(x);
-  const double magic = 6755399441055744.0;
-  double kd = fma(x, MPCB_FM_TWO_OVER_PI, magic);
-  int q = fm_lo32(kd);
-  double k = kd - magic;
-  double r = fma(-k, MPCB_FM_PIO2_1, x);
-  r = fma(-k, MPCB_FM_PIO2_2, r);
-  r = fma(-k, MPCB_FM_PIO2_3, r);
-  double z = r * r;
-  double v;
-  if (q & 1) v = fma(z * z, fm_poly_cos(z), fma(-0.5, z, 1.0));
-  else v = fma(r * z, fm_poly_sin(z), r);
-  return (q & 2) ? -v : v;
+  if (!(fabs(x) < MPCB_FM_TRIG_MAX)) return sin(x);
+  double s, c;
+  fm_sincos_nr(x, &s, &c);
+  return s;
 }
 
 // atan(x), all finite x (and +-Inf -> +-pi/2, NaN -> NaN).

@@ -32,33 +32,13 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     double a11, a12, a13, a21, a22, a23, a31, a32, a33;
     double bd, bl1, bl2, bl3;
   };
+  // Forces, outputs and (GRAD) the linearisation from the transcendental results: shared by both paths.
   template <bool GRAD>
-  static MPCB_DEV void call(const double* q, const StageU& su, const VehP& v, double* kp, double* kq, Lin& L) {
+  static MPCB_DEV void finish(const double* q, const StageU& su, const VehP& v, double s, double c, double a_f,
+                              double a_r, double zf, double zr, double stf, double ctf, double str_, double ctr,
+                              double sgn, double* kp, double* kq, Lin& L) {
     const double vx = q[1], vy = q[2], w = q[3];
-    double s, c;
-    fm_sincos(q[0], &s, &c);
-    const double a_f = fma(w, v.lf, vy), a_r = fma(w, v.lr, -vy);
-    double thf, ar;
-    if (vx > 0x1p-960 && vx < 0x1p960) {  // atan2(a, vx) = atan(a / vx) for vx > 0
-      double r = fm_rcp(vx);
-      thf = fm_atan(a_f * r);
-      ar = fm_atan(a_r * r);
-    } else {  // reversing / standstill / non-finite: library path
-      thf = atan2(a_f, vx);
-      ar = atan2(a_r, vx);
-    }
-    const double af = su.dl - thf;
-    const double sgn = vx > 0.0 ? 1.0 : (vx < 0.0 ? -1.0 : 0.0);
     const double frx = (v.cm1 - v.cm2 * vx) * su.d - v.cr0 * sgn - v.cr2 * vx * vx;
-    const double zf = v.bf * af, zr = v.br * ar;
-    double stf, ctf, str_, ctr;
-    if (GRAD) {
-      fm_sincos(v.cf * fm_atan(zf), &stf, &ctf);
-      fm_sincos(v.cr * fm_atan(zr), &str_, &ctr);
-    } else {
-      stf = fm_sin(v.cf * fm_atan(zf));
-      str_ = fm_sin(v.cr * fm_atan(zr));
-    }
     const double ffy = v.df * stf, fry = v.dr * str_;
     kp[0] = vx * c - vy * s;
     kp[1] = vx * s + vy * c;
@@ -71,8 +51,12 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
       const double Gf = v.df * ctf * v.cf * v.bf * fm_rcp(fma(zf, zf, 1.0));
       const double Gr = v.dr * ctr * v.cr * v.br * fm_rcp(fma(zr, zr, 1.0));
       const double vx2 = vx * vx;
-      const double idf = fm_rcp(fma(a_f, a_f, vx2)), idr = fm_rcp(fma(a_r, a_r, vx2));
-      // P*1 = G * d(atan2)/dvx (sign folded below), P*2 = G * d(atan2)/da
+      // d atan2 at the origin (standstill, no slip) is 0/0: use 0 there — the only place it can occur is the
+      // first call from a standstill start, whose state tangents are discarded (the oracle's reverse sweep
+      // never needs them either)
+      const double dnf = fma(a_f, a_f, vx2), dnr = fma(a_r, a_r, vx2);
+      const double idf = dnf > 0x1p-1000 ? fm_rcp(dnf) : 0.0, idr = dnr > 0x1p-1000 ? fm_rcp(dnr) : 0.0;
+      // P*1 = G * |d atan2/d vx|, P*2 = G * d atan2/d a
       const double Pf1 = Gf * a_f * idf, Pf2 = Gf * vx * idf;
       const double Pr1 = Gr * a_r * idr, Pr2 = Gr * vx * idr;
       const double sm = su.sdl * v.inv_m, cm = su.cdl * v.inv_m, lc = v.lf * su.cdl * v.inv_iz, lri = v.lr * v.inv_iz;
@@ -92,6 +76,59 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
       L.bl2 = gl * v.inv_m;
       L.bl3 = gl * v.lf * v.inv_iz;
     }
+  }
+  // Fast path: one branch-free block; the front and rear tyre chains run interleaved (ILP 2) next to
+  // the heading sincos.  Preconditions (checked by call): 0 < vx normal, |a_f|,|a_r| <= vx (SMALL:
+  // <= vx/2), su.z2_mode allows the second-stage kernels, |phi| < 2^17.
+  template <bool GRAD, bool SMALL>
+  static MPCB_DEV void call_fast(const double* q, const StageU& su, const VehP& v, double a_f, double a_r, double* kp,
+                                 double* kq, Lin& L) {
+    double s, c;
+    fm_sincos_nr(q[0], &s, &c);
+    const double r = fm_rcp(q[1]);
+    double thf, ar;
+    fm_atan_nr_x2<SMALL>(a_f * r, a_r * r, &thf, &ar);  // atan2(a, vx) = atan(a / vx) for vx > 0
+    const double af = su.dl - thf;
+    const double zf = v.bf * af, zr = v.br * ar;
+    double uf, ur;
+    fm_atan_nr_x2<SMALL>(zf, zr, &uf, &ur);
+    double stf, ctf = 0.0, str_, ctr = 0.0;
+    if (GRAD) fm_sincos_nr_x2(v.cf * uf, v.cr * ur, &stf, &ctf, &str_, &ctr);
+    else fm_sin_nr_x2(v.cf * uf, v.cr * ur, &stf, &str_);
+    finish<GRAD>(q, su, v, s, c, a_f, a_r, zf, zr, stf, ctf, str_, ctr, 1.0, kp, kq, L);
+  }
+  // General path: reversing / standstill / large slip / non-finite states.
+  template <bool GRAD>
+  static MPCB_DEV void call_slow(const double* q, const StageU& su, const VehP& v, double a_f, double a_r,
+                                              double* kp, double* kq, Lin& L) {
+    const double vx = q[1];
+    double s, c;
+    fm_sincos(q[0], &s, &c);
+    double thf, ar;
+    if (vx > 0x1p-960 && vx < 0x1p960) {
+      const double r = fm_rcp(vx);
+      thf = fm_atan(a_f * r);
+      ar = fm_atan(a_r * r);
+    } else {
+      thf = atan2(a_f, vx);
+      ar = atan2(a_r, vx);
+    }
+    const double af = su.dl - thf;
+    const double sgn = vx > 0.0 ? 1.0 : (vx < 0.0 ? -1.0 : 0.0);
+    const double zf = v.bf * af, zr = v.br * ar;
+    double stf, ctf, str_, ctr;
+    fm_sincos(v.cf * fm_atan(zf), &stf, &ctf);
+    fm_sincos(v.cr * fm_atan(zr), &str_, &ctr);
+    finish<GRAD>(q, su, v, s, c, a_f, a_r, zf, zr, stf, ctf, str_, ctr, sgn, kp, kq, L);
+  }
+  template <bool GRAD>
+  static MPCB_DEV void call(const double* q, const StageU& su, const VehP& v, double* kp, double* kq, Lin& L) {
+    const double vx = q[1];
+    const double a_f = fma(q[3], v.lf, q[2]), a_r = fma(q[3], v.lr, -q[2]);
+    const double am = fmax(fabs(a_f), fabs(a_r));
+    const bool ok = vx > 0x1p-960 && vx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX;
+    if (ok && su.z2_mode == 2 && am <= 0.5 * vx) call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
+    else call_slow<GRAD>(q, su, v, a_f, a_r, kp, kq, L);  // slip beyond atan(0.5) = 26.6 deg, reversing, ...
   }
   // tangent of one direction J at the same stage point: tq = (phi', vx', vy', w')
   template <int J>
@@ -159,76 +196,62 @@ template <int ND> struct ForDir<ND, ND> {
 
 // One RK4 element (car_dynamics.py:134-147) on p = (x, y), q = (phi, velocities), with tangents
 // tp[j] = (x', y'), tq[j] = q' of every direction j.  Position tangents never feed back, so they are
-// accumulated in place.
+// accumulated in place.  The four stages run as a rolled loop (stage point q + a_s k, weights b_s):
+// one copy of the model call instead of four keeps the kernels inside the instruction cache (the
+// unrolled form stalled 0.37 issue slots per instruction on no_instruction, profiles/r01_ncu_eval_v2b).
 template <int MODEL, bool GRAD>
 MPCB_DEV void rk4_fm(double* p, double* q, double (*tp)[2], double (*tq)[Fm<MODEL>::NQ], const StageU& su,
                      const VehP& v, double h) {
   using M = Fm<MODEL>;
   constexpr int NQ = M::NQ, ND = M::ND;
-  const double hh = 0.5 * h, h6 = h * (1.0 / 6.0), h3 = h * (1.0 / 3.0);
-  double kp[2], kq[NQ], accp[2], accq[NQ], sq[NQ];
-  double taq[GRAD ? ND : 1][NQ], tsq[GRAD ? ND : 1][NQ];
-  typename M::Lin L;
-  // stage 1
-  M::template call<GRAD>(q, su, v, kp, kq, L);
-  accp[0] = kp[0]; accp[1] = kp[1];
+  const double h6 = h * (1.0 / 6.0);
+  double kp[2] = {0.0, 0.0}, kq[NQ], accp[2] = {0.0, 0.0}, accq[NQ];
+  double tkq[GRAD ? ND : 1][NQ], taq[GRAD ? ND : 1][NQ];
 #pragma unroll
-  for (int i = 0; i < NQ; ++i) { accq[i] = kq[i]; sq[i] = fma(hh, kq[i], q[i]); }
+  for (int i = 0; i < NQ; ++i) { kq[i] = 0.0; accq[i] = 0.0; }
   if (GRAD) {
-    ForDir<0, ND>::run([&](auto J) {
-      constexpr int j = decltype(J)::value;
-      double tkp[2], tkq[NQ];
-      M::template tan<j>(L, tq[j], tkp, tkq);
-      tp[j][0] = fma(h6, tkp[0], tp[j][0]); tp[j][1] = fma(h6, tkp[1], tp[j][1]);
 #pragma unroll
-      for (int i = 0; i < NQ; ++i) { taq[j][i] = tkq[i]; tsq[j][i] = fma(hh, tkq[i], tq[j][i]); }
-    });
+    for (int j = 0; j < ND; ++j)
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) { tkq[j][i] = 0.0; taq[j][i] = 0.0; }
   }
-  // stage 2
-  M::template call<GRAD>(sq, su, v, kp, kq, L);
-  accp[0] = fma(2.0, kp[0], accp[0]); accp[1] = fma(2.0, kp[1], accp[1]);
+#pragma unroll 1
+  for (int s = 0; s < 4; ++s) {
+    const double a = s == 0 ? 0.0 : (s == 3 ? h : 0.5 * h);  // stage point  q + a k_prev
+    const double bw = (s == 0 || s == 3) ? 1.0 : 2.0;        // weight of k_s
+    double sq[NQ];
 #pragma unroll
-  for (int i = 0; i < NQ; ++i) { accq[i] = fma(2.0, kq[i], accq[i]); sq[i] = fma(hh, kq[i], q[i]); }
-  if (GRAD) {
-    ForDir<0, ND>::run([&](auto J) {
-      constexpr int j = decltype(J)::value;
-      double tkp[2], tkq[NQ];
-      M::template tan<j>(L, tsq[j], tkp, tkq);
-      tp[j][0] = fma(h3, tkp[0], tp[j][0]); tp[j][1] = fma(h3, tkp[1], tp[j][1]);
+    for (int i = 0; i < NQ; ++i) sq[i] = fma(a, kq[i], q[i]);
+    typename M::Lin L;
+    M::template call<GRAD>(sq, su, v, kp, kq, L);
+    accp[0] = fma(bw, kp[0], accp[0]);
+    accp[1] = fma(bw, kp[1], accp[1]);
 #pragma unroll
-      for (int i = 0; i < NQ; ++i) { taq[j][i] = fma(2.0, tkq[i], taq[j][i]); tsq[j][i] = fma(hh, tkq[i], tq[j][i]); }
-    });
+    for (int i = 0; i < NQ; ++i) accq[i] = fma(bw, kq[i], accq[i]);
+    if (GRAD) {
+      const double wp = bw * h6;
+      ForDir<0, ND>::run([&](auto J) {
+        constexpr int j = decltype(J)::value;
+        double tsq[NQ], tkp[2], tk[NQ];
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) tsq[i] = fma(a, tkq[j][i], tq[j][i]);
+        M::template tan<j>(L, tsq, tkp, tk);
+        tp[j][0] = fma(wp, tkp[0], tp[j][0]);
+        tp[j][1] = fma(wp, tkp[1], tp[j][1]);
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) { tkq[j][i] = tk[i]; taq[j][i] = fma(bw, tk[i], taq[j][i]); }
+      });
+    }
   }
-  // stage 3
-  M::template call<GRAD>(sq, su, v, kp, kq, L);
-  accp[0] = fma(2.0, kp[0], accp[0]); accp[1] = fma(2.0, kp[1], accp[1]);
+  p[0] = fma(h6, accp[0], p[0]);
+  p[1] = fma(h6, accp[1], p[1]);
 #pragma unroll
-  for (int i = 0; i < NQ; ++i) { accq[i] = fma(2.0, kq[i], accq[i]); sq[i] = fma(h, kq[i], q[i]); }
+  for (int i = 0; i < NQ; ++i) q[i] = fma(h6, accq[i], q[i]);
   if (GRAD) {
-    ForDir<0, ND>::run([&](auto J) {
-      constexpr int j = decltype(J)::value;
-      double tkp[2], tkq[NQ];
-      M::template tan<j>(L, tsq[j], tkp, tkq);
-      tp[j][0] = fma(h3, tkp[0], tp[j][0]); tp[j][1] = fma(h3, tkp[1], tp[j][1]);
 #pragma unroll
-      for (int i = 0; i < NQ; ++i) { taq[j][i] = fma(2.0, tkq[i], taq[j][i]); tsq[j][i] = fma(h, tkq[i], tq[j][i]); }
-    });
-  }
-  // stage 4
-  M::template call<GRAD>(sq, su, v, kp, kq, L);
-  p[0] = fma(h6, accp[0] + kp[0], p[0]);
-  p[1] = fma(h6, accp[1] + kp[1], p[1]);
+    for (int j = 0; j < ND; ++j)
 #pragma unroll
-  for (int i = 0; i < NQ; ++i) q[i] = fma(h6, accq[i] + kq[i], q[i]);
-  if (GRAD) {
-    ForDir<0, ND>::run([&](auto J) {
-      constexpr int j = decltype(J)::value;
-      double tkp[2], tkq[NQ];
-      M::template tan<j>(L, tsq[j], tkp, tkq);
-      tp[j][0] = fma(h6, tkp[0], tp[j][0]); tp[j][1] = fma(h6, tkp[1], tp[j][1]);
-#pragma unroll
-      for (int i = 0; i < NQ; ++i) tq[j][i] = fma(h6, taq[j][i] + tkq[i], tq[j][i]);
-    });
+      for (int i = 0; i < NQ; ++i) tq[j][i] = fma(h6, taq[j][i], tq[j][i]);
   }
 }
 

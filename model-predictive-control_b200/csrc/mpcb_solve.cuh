@@ -4,13 +4,30 @@
 // StructuredPANOCLBFGSSolver calling CasADi-generated f/grad_f.  Canonical algorithm: SURVEY.md
 // Appendix A (restated on the CPU in oracle/orc_solver.hpp).
 //
-// Mapping ("instance-per-lane"): every lane owns one MPC instance and walks a small state machine.
-// All lanes of a warp meet at ONE evaluation site per loop trip (forward rollout, plus the reverse
-// sweep for the lanes that asked for a gradient), so the dominant fp64 work never diverges even
-// though each lane is at a different PANOC iteration / line-search trial.  Finished lanes pull the
-// next instance from a global queue (iteration counts vary 10x between instances).  Per-lane
-// vectors (iterates, L-BFGS history, checkpoints) live in a lane-interleaved workspace so a warp's
-// accesses to element i of 32 instances are one 256-byte coalesced transaction.
+// Mapping ("lane tile per instance").  One solve is a chain of ~300 dependent rollouts, each a chain
+// of 16 N dependent model calls: the kernel is bound by that latency, not by throughput, until the
+// batch exceeds ~20 k instances per GPU.  A tile of G lanes (G = 8, 4, 2, 1, picked by the host from
+// the batch size) therefore owns one instance and spends its spare lanes on SPECULATION that removes
+// evaluations from the dependent chain:
+//   * line search: lane j evaluates the candidate tau = 2^-j (all 8 back-tracking trials of
+//     Appendix A 3d at once for G = 8), then its own psi(x̂+); the first accepted candidate in
+//     sequential order wins — the same decisions as sequential back-tracking because every trial
+//     restarts from the iterate's (L, gamma);
+//   * descent lemma at k = 0: lane j evaluates psi(x̂(gamma / 2^j));
+//   * Lipschitz estimate: lane 1 evaluates grad psi(x + h) while lane 0 evaluates grad psi(x).
+// Every lane of a tile runs the same state machine on the same data (redundantly — free in SIMT), so
+// control flow is tile-uniform; per-lane candidate results only enter through tile ballots/shuffles.
+// All lanes of a warp meet at ONE evaluation site per loop trip, so the dominant fp64 work never
+// diverges even though tiles are at different PANOC iterations.  Finished tiles pull the next
+// instance from a global queue.
+//
+// Workspace.  Per-lane rows (iterate banks, candidate, stage Jacobians) are lane-interleaved: a
+// warp's access to element i of 32 lanes is one 256-byte transaction.  Per-tile vectors (q, L-BFGS
+// history) use a tile-vector layout in which the G lanes of a tile own G consecutive doubles, so the
+// two-loop recursion is split over the lanes with coalesced accesses and tile-shuffle dot products.
+// Locations shared by a tile are either written by their owner lane, or written by every lane with
+// the same value that does not depend on the old content; read-modify-writes are done by lane 0
+// between tile barriers.
 #pragma once
 #include <float.h>
 #include "mpcb_fwd.cuh"
@@ -24,41 +41,51 @@ struct SolveArgs {
   double *U, *lam;
   int32_t *status, *iters, *evals;
   double *psi, *res;
-  double* ws;
-  int32_t* wsi;
-  int64_t ns;
+  double* ws;    // per-lane rows   [LaneMap.total, ns]
+  double* wst;   // per-tile data   [TileMap.total, nt] (tile-vector region first, plain rows after)
+  int64_t ns, nt;
   unsigned long long* queue;
 };
 
 enum SolveState {
-  ST_IDLE = 0, ST_START_PANOC, ST_INIT_G, ST_LIP_G, ST_XHAT_V, ST_ITER_TOP, ST_FD_G, ST_LS_START, ST_LS_TRIAL,
-  ST_LS_G, ST_LS_V, ST_PANOC_EXIT, ST_ALM_V, ST_ALM_UPDATE
+  ST_IDLE = 0, ST_START_PANOC, ST_INIT_G1, ST_LIP_DONE, ST_XHAT_REQ, ST_XHAT_DONE, ST_ITER_TOP, ST_FD_DONE,
+  ST_LS_START, ST_LS_REQ, ST_LS_G_DONE, ST_LS_V_DONE, ST_PANOC_EXIT, ST_ALM_V, ST_ALM_UPDATE
 };
 
-// Workspace row map (units: doubles per lane).
-struct WsMap {
-  int n, mem;
-  int Q, XE, GE, XB, LS, LY, AL, RH, CHK, ST, SIG, E1, E2, total;
-  __host__ __device__ WsMap(int n_, int mem_, int N, int n_sub, int nx, int m) : n(n_), mem(mem_) {
-    Q = 8 * n; XE = 9 * n; GE = 10 * n; XB = 11 * n;
-    LS = 12 * n; LY = LS + mem * n; AL = LY + mem * n; RH = AL + mem;
-    CHK = RH + mem; ST = CHK + N * (nx * (nx - 1) + 2 + nx); SIG = ST + N * nx; E1 = SIG + m; E2 = E1 + m; total = E2 + m;
+// Per-lane workspace rows (units: doubles per lane).
+struct LaneMap {
+  int n, SCR, ST, total;
+  __host__ __device__ LaneMap(int n_, int N, int nx, int stage_doubles, bool bounded) : n(n_) {
+    SCR = 8 * n; ST = SCR + N * stage_doubles; total = ST + (bounded ? N * nx : 0);
   }
   __host__ __device__ int X(int bank) const { return bank * 4 * n; }
   __host__ __device__ int G(int bank) const { return bank * 4 * n + n; }
   __host__ __device__ int XH(int bank) const { return bank * 4 * n + 2 * n; }
   __host__ __device__ int P(int bank) const { return bank * 4 * n + 3 * n; }
 };
+// Per-tile workspace (units: doubles per tile).  The first `vec_total` doubles are tile-vectors of
+// padded length np (Q, XB, S_0.., Y_0..); the rest are plain per-tile rows.
+struct TileMap {
+  int np, Q, XB, LS, LY, vec_total, AL, RH, SIG, E1, E2, total;
+  __host__ __device__ TileMap(int n, int G, int mem, int m, bool bounded) {
+    np = (n + G - 1) / G * G;
+    Q = 0; XB = np; LS = 2 * np; LY = LS + mem * np; vec_total = LY + mem * np;
+    AL = vec_total; RH = AL + mem; SIG = RH + mem;
+    E1 = SIG + (bounded ? m : 0); E2 = E1 + (bounded ? m : 0); total = E2 + (bounded ? m : 0);
+  }
+};
 
-template <int MODEL>
-__global__ void __launch_bounds__(128)
+template <int MODEL, int G>
+__global__ void __launch_bounds__(64)
 k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
-  constexpr int NX = ModelTraits<MODEL>::NX;
+  constexpr int NX = Fm<MODEL>::NX;
+  constexpr int K = fm_stage_doubles<MODEL>();
   extern __shared__ double smem[];
   __shared__ VehP v;
   const int n = d.n, m = d.m, mem = sp.lbfgs_mem;
   double* sroad = smem;
   double* sbox = smem + (a.ra.in_smem ? a.ra.R * d.S * 2 : 0);  // lb[n], ub[n]
+  fm_load_smem();
   if (threadIdx.x == 0) load_vehicle(&v, a.p, d);
   if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
   for (int i = threadIdx.x; i < n; i += blockDim.x) { sbox[i] = a.lb[i]; sbox[n + i] = a.ub[i]; }
@@ -66,30 +93,53 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   const double* lbv = sbox;
   const double* ubv = sbox + n;
 
-  const int64_t ns = a.ns;
+  const int64_t ns = a.ns, nt = a.nt;
   const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const WsMap M(n, mem, d.N, d.n_sub, NX, m);
-  auto W = [&](int row) { return Vec{a.ws + (int64_t)row * ns + slot, ns}; };
-  const Vec scr = W(M.CHK);  // stage Jacobians of the forward-mode evaluation
+  const int lane = threadIdx.x & 31;
+  const int l = lane % G;  // lane within the tile
+  const int tbase = lane - l;
+  const unsigned tmask = ((G >= 32) ? 0xffffffffu : ((1u << G) - 1u)) << tbase;
+  const int64_t tile = slot / G;
+  const LaneMap M(n, d.N, NX, K, d.bounded != 0);
+  const TileMap T(n, G, mem, m, d.bounded != 0);
+  const int ne = T.np / G;  // tile-vector elements owned by each lane: e = l + G j
+  // row `row` of tile lane `ll` (lane-interleaved)
+  auto WL = [&](int row, int ll) { return Vec{a.ws + (int64_t)row * ns + (slot - l + ll), ns}; };
+  // element i of the tile-vector at offset `off` (off is a multiple of G)
+  auto tv = [&](int off, int i) -> double& { return a.wst[((int64_t)((off + i) / G) * nt + tile) * G + (i % G)]; };
+  double* const trow = a.wst + (int64_t)T.vec_total * nt;  // plain per-tile rows
+  auto TR = [&](int off, int i) -> double& { return trow[(int64_t)(off - T.vec_total + i) * nt + tile]; };
+  auto tsync = [&]() { __syncwarp(tmask); };
+  auto tsum = [&](double x) {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) x += __shfl_xor_sync(tmask, x, o);
+    return x;
+  };
+  auto tbcast = [&](double x, int src) { return __shfl_sync(tmask, x, tbase + src); };
 
-  // ---- per-lane registers ----
-  int state = ST_IDLE, want = 0, ep = 0, eg = 0;
+  // ---- tile-uniform registers ----
+  int state = ST_IDLE;
   bool exhausted = false;
   int64_t b = -1;
-  int bank = 0, k = 0, no_prog = 0, lb_idx = 0, lb_full = 0;
-  double psi = 0, psi_hat = 0, gTp = 0, pTp = 0, L = 0, gam = 0, phi = 0, tau = 0, sigma = 0, hfd = 0, hh = 0;
-  double psi_n = 0, gTp_n = 0, pTp_n = 0, L_n = 0, gam_n = 0;
-  double eps_tol = 0, peps = 0, ppsi = 0, norm_e2 = 0, val = 0;
-  int alm_i = 0, inner_total = 0, n_val = 0, n_grad = 0, pstatus = 0;
+  int cl = 0, cb = 0;  // the iterate (x, g, x̂, p) lives in lane cl's bank cb
+  int k = 0, no_prog = 0, lb_idx = 0, lb_full = 0, hb = 0, lsb = 0;
+  double psi = 0, psi_hat = 0, gTp = 0, pTp = 0, L = 0, gam = 0, phi = 0, tau0 = 0, sigma = 0, hfd = 0, hh = 0;
+  double eps_tol = 0, peps = 0, ppsi = 0, norm_e2 = 0;
+  int alm_i = 0, inner_total = 0, pstatus = 0;
   unsigned long long mask0 = 0, mask1 = 0;  // inactive-set bitmask (n <= 128)
   auto mbit = [&](int j) { return j < 64 ? (mask0 >> j) & 1ull : (mask1 >> (j - 64)) & 1ull; };
+  // ---- per-lane registers (this lane's candidate / evaluation request) ----
+  int want = 0, n_val = 0, n_grad = 0;
+  Vec evp{nullptr, 0}, evg{nullptr, 0};
+  double val = 0;
+  bool c_valid = false, c_pend = false, c_rq = false, c_fb = false, c_acc = false;
+  double psi_n = 0, psi_hat_n = 0, gTp_n = 0, pTp_n = 0, L_n = 0, gam_n = 0, phi_n = 0;
 
-  // x̂ = Π_C(x − γ g), p = x̂ − x; also gᵀp and pᵀp (sequential sums, same order as the oracle)
-  auto prox = [&](int xr, int gr, double gamma, int xhr, int pr, double& gtp, double& ptp) {
-    Vec X = W(xr), G = W(gr), XH = W(xhr), P = W(pr);
+  // x̂ = Π_C(x − γ g), p = x̂ − x (stored into XH, P); returns gᵀp and pᵀp
+  auto prox = [&](const Vec& X, const Vec& Gv, double gamma, const Vec& XH, const Vec& P, double& gtp, double& ptp) {
     double s1 = 0.0, s2 = 0.0;
     for (int i = 0; i < n; ++i) {
-      double xi = X(i), gi = G(i);
+      double xi = X(i), gi = Gv(i);
       double t = xi - gamma * gi;
       t = t < lbv[i] ? lbv[i] : (t > ubv[i] ? ubv[i] : t);
       double pi = t - xi;
@@ -102,112 +152,177 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     ptp = s2;
   };
 
-  // q <- H q on the inactive set (masked two-loop recursion, Appendix A 3c)
+  // q <- H q on the inactive set (masked two-loop recursion, Appendix A 3c), split over the tile.
   auto lbfgs_apply = [&]() {
-    Vec Q = W(M.Q), AL = W(M.AL), RH = W(M.RH);
     const int cnt = lb_full ? mem : lb_idx;
     double H0 = -1.0;
     for (int kk = 0; kk < cnt; ++kk) {
       int i = lb_idx - 1 - kk;
       if (i < 0) i += mem;
-      Vec S = W(M.LS + i * n), Y = W(M.LY + i * n);
       double sy = 0.0, yy = 0.0, sq = 0.0;
-      for (int j = 0; j < n; ++j)
-        if (mbit(j)) { double s = S(j), y = Y(j); sy += s * y; yy += y * y; sq += s * Q(j); }
-      if (!(sy > 0.0)) { RH.set(i, nan("")); continue; }
+      for (int j = 0; j < ne; ++j) {
+        int e = l + G * j;
+        if (e < n && mbit(e)) {
+          double s = tv(T.LS + i * T.np, e), y = tv(T.LY + i * T.np, e);
+          sy += s * y; yy += y * y; sq += s * tv(T.Q, e);
+        }
+      }
+      sy = tsum(sy); yy = tsum(yy); sq = tsum(sq);
+      if (!(sy > 0.0)) { TR(T.RH, i) = nan(""); continue; }
       double rho = 1.0 / sy;
-      RH.set(i, rho);
+      TR(T.RH, i) = rho;
       if (H0 < 0.0) H0 = sy / yy;
       double al = rho * sq;
-      AL.set(i, al);
-      for (int j = 0; j < n; ++j)
-        if (mbit(j)) Q.set(j, Q(j) - al * Y(j));
+      TR(T.AL, i) = al;
+      for (int j = 0; j < ne; ++j) {
+        int e = l + G * j;
+        if (e < n && mbit(e)) tv(T.Q, e) -= al * tv(T.LY + i * T.np, e);
+      }
     }
     if (!(H0 >= 0.0)) H0 = gam;
-    for (int j = 0; j < n; ++j)
-      if (mbit(j)) Q.set(j, Q(j) * H0);
+    for (int j = 0; j < ne; ++j) {
+      int e = l + G * j;
+      if (e < n && mbit(e)) tv(T.Q, e) *= H0;
+    }
     for (int kk = cnt - 1; kk >= 0; --kk) {
       int i = lb_idx - 1 - kk;
       if (i < 0) i += mem;
-      double rho = RH(i);
+      double rho = TR(T.RH, i);
       if (isnan(rho)) continue;
-      Vec S = W(M.LS + i * n), Y = W(M.LY + i * n);
       double yq = 0.0;
-      for (int j = 0; j < n; ++j)
-        if (mbit(j)) yq += Y(j) * Q(j);
-      double coef = AL(i) - rho * yq;
-      for (int j = 0; j < n; ++j)
-        if (mbit(j)) Q.set(j, Q(j) + coef * S(j));
+      for (int j = 0; j < ne; ++j) {
+        int e = l + G * j;
+        if (e < n && mbit(e)) yq += tv(T.LY + i * T.np, e) * tv(T.Q, e);
+      }
+      yq = tsum(yq);
+      double coef = TR(T.AL, i) - rho * yq;
+      for (int j = 0; j < ne; ++j) {
+        int e = l + G * j;
+        if (e < n && mbit(e)) tv(T.Q, e) += coef * tv(T.LS + i * T.np, e);
+      }
     }
   };
 
+  // write the instance's results (from the backup x when the solve failed numerically)
+  auto finish_instance = [&](int fin_status, bool from_backup) {
+    int nv = n_val, ng = n_grad;
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) { nv += __shfl_xor_sync(tmask, nv, o); ng += __shfl_xor_sync(tmask, ng, o); }
+    if (l == 0) {
+      Vec X0 = WL(M.X(0), 0);
+      for (int i = 0; i < n; ++i) a.U[b * n + i] = from_backup ? tv(T.XB, i) : X0(i);
+      a.status[b] = fin_status;
+      a.iters[2 * b] = alm_i + 1; a.iters[2 * b + 1] = inner_total;
+      a.evals[2 * b] = nv; a.evals[2 * b + 1] = ng;
+      a.psi[b] = ppsi; a.res[b] = peps;
+    }
+    n_val = 0; n_grad = 0;
+  };
+
   for (;;) {
-    // ================= transition phase: run the lane's state machine up to its next evaluation ==
+    // ================= transition phase: run the tile's state machine up to its next evaluation ====
     want = 0;
     for (;;) {
       if (state == ST_IDLE) {
         if (exhausted) break;
-        b = (int64_t)atomicAdd(a.queue, 1ull);
-        if (b >= a.B) { exhausted = true; break; }
+        long long bb = 0;
+        if (l == 0) bb = (long long)atomicAdd(a.queue, 1ull);
+        bb = __shfl_sync(tmask, bb, tbase);
+        if (bb >= a.B) { exhausted = true; break; }
+        b = bb;
         // controller.py:20-21,57: warm start (U, λ) comes in through U_inout / lambda_inout
-        Vec X = W(M.X(0));
-        for (int i = 0; i < n; ++i) X.set(i, a.U[b * n + i]);
-        bank = 0;
+        cl = 0; cb = 0;
+        if (l == 0) {
+          Vec X = WL(M.X(0), 0);
+          for (int i = 0; i < n; ++i) X.set(i, a.U[b * n + i]);
+        }
+        tsync();
         eps_tol = sp.eps0;
         alm_i = 0; inner_total = 0; n_val = 0; n_grad = 0;
         if (d.bounded) {
-          Vec SG = W(M.SIG), E1 = W(M.E1);
-          for (int r = 0; r < m; ++r) { SG.set(r, sp.Sigma0); E1.set(r, 0.0); }
+          for (int r = 0; r < m; ++r) { TR(T.SIG, r) = sp.Sigma0; TR(T.E1, r) = 0.0; }
         }
         state = ST_START_PANOC;
       } else if (state == ST_START_PANOC) {
         if (d.bounded) {  // clamp multipliers to ±M, 0 on infinite sides
-          for (int r = 0; r < m; ++r) {
-            double lo = isinf(d.D_lo[r % NX]) ? 0.0 : -sp.M, hi = isinf(d.D_hi[r % NX]) ? 0.0 : sp.M;
-            double lv = a.lam[b * m + r];
-            a.lam[b * m + r] = lv < lo ? lo : (lv > hi ? hi : lv);
+          if (l == 0) {
+            for (int r = 0; r < m; ++r) {
+              double lo = isinf(d.D_lo[r % NX]) ? 0.0 : -sp.M, hi = isinf(d.D_hi[r % NX]) ? 0.0 : sp.M;
+              double lv = a.lam[b * m + r];
+              a.lam[b * m + r] = lv < lo ? lo : (lv > hi ? hi : lv);
+            }
           }
+          tsync();
         }
-        Vec X = W(M.X(bank)), XB = W(M.XB);
-        for (int i = 0; i < n; ++i) XB.set(i, X(i));
-        k = 0; no_prog = 0; lb_idx = 0; lb_full = 0;
-        ep = M.X(bank); eg = M.G(bank); want = 2;
-        state = ST_INIT_G;
-        break;
-      } else if (state == ST_INIT_G) {
-        psi = val;
-        Vec X = W(M.X(bank)), XE = W(M.XE);
+        Vec X = WL(M.X(cb), cl);
+        // the Lipschitz probe point x + h goes to the probing lane's free bank
+        const int pl = G >= 2 ? 1 : 0;
+        Vec XE = WL(M.X(cb ^ 1), pl);
         hh = 0.0;
         for (int i = 0; i < n; ++i) {
           double xi = X(i);
+          tv(T.XB, i) = xi;
           double h = fmax(fabs(xi) * sp.lip_eps, sp.lip_delta);
-          XE.set(i, xi + h);
+          if (l == pl) XE.set(i, xi + h);
           hh += h * h;
         }
-        ep = M.XE; eg = M.GE; want = 2;
-        state = ST_LIP_G;
+        k = 0; no_prog = 0; lb_idx = 0; lb_full = 0;
+        if (G >= 2) {
+          if (l == 0) { evp = X; evg = WL(M.G(cb), cl); want = 2; }
+          else if (l == 1) { evp = XE; evg = WL(M.G(cb ^ 1), 1); want = 2; }
+          state = ST_LIP_DONE;
+        } else {
+          evp = X; evg = WL(M.G(cb), cl); want = 2;
+          state = ST_INIT_G1;
+        }
         break;
-      } else if (state == ST_LIP_G) {
-        Vec G = W(M.G(bank)), GE = W(M.GE);
+      } else if (state == ST_INIT_G1) {  // G == 1 only: second gradient of the Lipschitz estimate
+        psi = val;
+        evp = WL(M.X(cb ^ 1), 0); evg = WL(M.G(cb ^ 1), 0); want = 2;
+        state = ST_LIP_DONE;
+        break;
+      } else if (state == ST_LIP_DONE) {
+        if (G >= 2) psi = tbcast(val, 0);
+        const int pl = G >= 2 ? 1 : 0;
+        Vec Gc = WL(M.G(cb), cl), GE = WL(M.G(cb ^ 1), pl);
         double dd = 0.0;
-        for (int i = 0; i < n; ++i) { double t = GE(i) - G(i); dd += t * t; }
+        for (int i = 0; i < n; ++i) { double t = GE(i) - Gc(i); dd += t * t; }
         L = sqrt(dd) / sqrt(hh);
         if (!isfinite(L)) { pstatus = MPCB_STATUS_NOT_FINITE; peps = nan(""); ppsi = psi; state = ST_PANOC_EXIT; continue; }
         L = L < sp.L_min ? sp.L_min : (L > sp.L_max ? sp.L_max : L);
         gam = sp.Lgamma_factor / L;
-        prox(M.X(bank), M.G(bank), gam, M.XH(bank), M.P(bank), gTp, pTp);
-        ep = M.XH(bank); want = 1;
-        state = ST_XHAT_V;
-        break;
-      } else if (state == ST_XHAT_V) {
-        psi_hat = val;
-        double margin = (1.0 + fabs(psi)) * sp.quad_tol;
-        if (psi_hat - psi > gTp + 0.5 * L * pTp + margin && L * 2.0 <= sp.L_max) {  // descent lemma, k = 0
-          L *= 2.0; gam *= 0.5;
-          prox(M.X(bank), M.G(bank), gam, M.XH(bank), M.P(bank), gTp, pTp);
-          ep = M.XH(bank); want = 1;
-          break;
+        hb = 0;
+        state = ST_XHAT_REQ;
+      } else if (state == ST_XHAT_REQ) {
+        // descent lemma at k = 0 (Appendix A 3a): candidate c has halved gamma c times
+        const int c = hb * G + l;
+        L_n = ldexp(L, c); gam_n = ldexp(gam, -c);
+        c_valid = c == 0 || L_n <= sp.L_max;
+        if (c_valid) {
+          prox(WL(M.X(cb), cl), WL(M.G(cb), cl), gam_n, WL(M.XH(cb ^ 1), l), WL(M.P(cb ^ 1), l), gTp_n, pTp_n);
+          evp = WL(M.XH(cb ^ 1), l); want = 1;
         }
+        state = ST_XHAT_DONE;
+        break;
+      } else if (state == ST_XHAT_DONE) {
+        bool done = false;
+        if (c_valid) {
+          psi_hat_n = val;
+          double margin = (1.0 + fabs(psi)) * sp.quad_tol;
+          bool violated = psi_hat_n - psi > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max;
+          done = !violated;
+        }
+        const unsigned dm = (__ballot_sync(tmask, done) & tmask) >> tbase;
+        if (!dm) { ++hb; state = ST_XHAT_REQ; continue; }
+        const int jw = __ffs(dm) - 1;
+        L = tbcast(L_n, jw); gam = tbcast(gam_n, jw);
+        gTp = tbcast(gTp_n, jw); pTp = tbcast(pTp_n, jw);
+        psi_hat = tbcast(psi_hat_n, jw);
+        if (l == jw) {  // the winner's x̂, p become the iterate's
+          Vec XHs = WL(M.XH(cb ^ 1), l), Ps = WL(M.P(cb ^ 1), l), XHd = WL(M.XH(cb), cl), Pd = WL(M.P(cb), cl);
+          for (int i = 0; i < n; ++i) { XHd.set(i, XHs(i)); Pd.set(i, Ps(i)); }
+        }
+        tsync();
         phi = psi + pTp / (2.0 * gam) + gTp;
         state = ST_ITER_TOP;
       } else if (state == ST_ITER_TOP) {
@@ -220,146 +335,191 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         if (stop) { pstatus = stop; peps = eps_k; ppsi = psi_hat; state = ST_PANOC_EXIT; continue; }
         if (k == 0) { state = ST_LS_START; continue; }
         // direction (Appendix A 3c)
-        Vec X = W(M.X(bank)), G = W(M.G(bank)), P = W(M.P(bank)), Q = W(M.Q);
+        Vec X = WL(M.X(cb), cl), Gc = WL(M.G(cb), cl), P = WL(M.P(cb), cl);
         int nJ = 0;
         mask0 = 0; mask1 = 0;
-        for (int i = 0; i < n; ++i) {
-          double gd = X(i) - gam * G(i);
-          bool active = gd < lbv[i] || ubv[i] < gd;
-          if (!active) { ++nJ; if (i < 64) mask0 |= 1ull << i; else mask1 |= 1ull << (i - 64); }
-        }
-        bool use_fd = sp.hess_vec_fd && nJ > 0 && nJ < n;
         double xx = 0.0;
         for (int i = 0; i < n; ++i) {
           double xi = X(i);
+          double gd = xi - gam * Gc(i);
+          bool active = gd < lbv[i] || ubv[i] < gd;
+          if (!active) { ++nJ; if (i < 64) mask0 |= 1ull << i; else mask1 |= 1ull << (i - 64); }
           xx += xi * xi;
-          Q.set(i, mbit(i) ? (use_fd ? 0.0 : -G(i)) : P(i));
+        }
+        const bool use_fd = sp.hess_vec_fd && nJ > 0 && nJ < n;
+        for (int j = 0; j < ne; ++j) {
+          int e = l + G * j;
+          if (e < n) tv(T.Q, e) = mbit(e) ? (use_fd ? 0.0 : -Gc(e)) : P(e);
         }
         if (use_fd) {
           hfd = 6.0554544523933395e-06 /* cbrt(DBL_EPSILON) */ * (1.0 + sqrt(xx));
-          Vec XE = W(M.XE);
-          for (int i = 0; i < n; ++i) XE.set(i, X(i) + hfd * Q(i));
-          ep = M.XE; eg = M.GE; want = 2;
-          state = ST_FD_G;
+          if (l == 0) {  // q is p on the active set and 0 on the inactive set at this point
+            Vec XE = WL(M.X(cb ^ 1), 0);
+            for (int i = 0; i < n; ++i) XE.set(i, X(i) + hfd * (mbit(i) ? 0.0 : P(i)));
+            evp = XE; evg = WL(M.G(cb ^ 1), 0); want = 2;
+          }
+          state = ST_FD_DONE;
           break;
         }
         if (nJ > 0) lbfgs_apply();
+        tsync();  // every lane reads the whole q next
         state = ST_LS_START;
-      } else if (state == ST_FD_G) {
-        Vec G = W(M.G(bank)), GE = W(M.GE), Q = W(M.Q);
-        for (int i = 0; i < n; ++i)
-          if (mbit(i)) { double gi = G(i); Q.set(i, -gi - (GE(i) - gi) / hfd); }
+      } else if (state == ST_FD_DONE) {
+        Vec Gc = WL(M.G(cb), cl), GE = WL(M.G(cb ^ 1), 0);
+        for (int j = 0; j < ne; ++j) {
+          int e = l + G * j;
+          if (e < n && mbit(e)) { double gi = Gc(e); tv(T.Q, e) = -gi - (GE(e) - gi) / hfd; }
+        }
         lbfgs_apply();
+        tsync();
         state = ST_LS_START;
       } else if (state == ST_LS_START) {
-        tau = 0.0;
+        tau0 = 0.0;
         if (k > 0) {
-          tau = 1.0;
-          Vec Q = W(M.Q);
+          tau0 = 1.0;
           bool fin = true;
-          for (int i = 0; i < n; ++i) fin = fin && isfinite(Q(i));
-          if (!fin) { tau = 0.0; lb_idx = 0; lb_full = 0; }
+          for (int i = 0; i < n; ++i) fin = fin && isfinite(tv(T.Q, i));
+          if (!fin) { tau0 = 0.0; lb_idx = 0; lb_full = 0; }
         }
         sigma = (1.0 - gam * L) * pTp / (2.0 * gam);
-        state = ST_LS_TRIAL;
-      } else if (state == ST_LS_TRIAL) {
-        L_n = L; gam_n = gam;
-        const int nb = bank ^ 1;
-        Vec X = W(M.X(bank)), XN = W(M.X(nb));
-        if (tau * 0.5 < sp.tau_min) {
-          Vec XH = W(M.XH(bank));
-          for (int i = 0; i < n; ++i) XN.set(i, XH(i));
-        } else {
-          Vec P = W(M.P(bank)), Q = W(M.Q);
-          for (int i = 0; i < n; ++i) XN.set(i, X(i) + (1.0 - tau) * P(i) + tau * Q(i));
+        lsb = 0;
+        state = ST_LS_REQ;
+      } else if (state == ST_LS_REQ) {
+        // line-search candidates (Appendix A 3d): c = 0..7 -> tau = 2^-c, c = 8 -> the prox step x̂
+        // (forced accept); tau0 = 0 (k = 0 or non-finite q) -> only the prox step.
+        const int c = lsb * G + l;
+        const int nb = cb ^ 1;
+        c_fb = tau0 == 0.0 ? true : c == 8;
+        c_valid = tau0 == 0.0 ? c == 0 : c <= 8;
+        c_pend = c_valid; c_rq = c_valid; c_acc = false;
+        if (c_valid) {
+          Vec XN = WL(M.X(nb), l);
+          if (c_fb) {
+            Vec XH = WL(M.XH(cb), cl);
+            for (int i = 0; i < n; ++i) XN.set(i, XH(i));
+          } else {
+            const double tau = ldexp(1.0, -c);
+            Vec X = WL(M.X(cb), cl), P = WL(M.P(cb), cl);
+            for (int i = 0; i < n; ++i) XN.set(i, X(i) + (1.0 - tau) * P(i) + tau * tv(T.Q, i));
+          }
+          evp = XN; evg = WL(M.G(nb), l); want = 2;
         }
-        ep = M.X(nb); eg = M.G(nb); want = 2;
-        state = ST_LS_G;
+        state = ST_LS_G_DONE;
         break;
-      } else if (state == ST_LS_G) {
-        psi_n = val;
-        const int nb = bank ^ 1;
-        prox(M.X(nb), M.G(nb), gam_n, M.XH(nb), M.P(nb), gTp_n, pTp_n);
-        ep = M.XH(nb); want = 1;
-        state = ST_LS_V;
+      } else if (state == ST_LS_G_DONE) {
+        const int nb = cb ^ 1;
+        if (c_valid) {
+          psi_n = val;
+          L_n = L; gam_n = gam;
+          prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
+          evp = WL(M.XH(nb), l); want = 1;
+        }
+        state = ST_LS_V_DONE;
         break;
-      } else if (state == ST_LS_V) {
-        const int nb = bank ^ 1;
-        double psi_hat_n = val;
-        double margin = (1.0 + fabs(psi_n)) * sp.quad_tol;
-        if (psi_hat_n - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max) {
-          L_n *= 2.0; gam_n *= 0.5;
-          prox(M.X(nb), M.G(nb), gam_n, M.XH(nb), M.P(nb), gTp_n, pTp_n);
-          ep = M.XH(nb); want = 1;
+      } else if (state == ST_LS_V_DONE) {
+        const int nb = cb ^ 1;
+        if (c_valid && c_pend && c_rq) {
+          psi_hat_n = val;
+          double margin = (1.0 + fabs(psi_n)) * sp.quad_tol;
+          if (psi_hat_n - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max) {
+            L_n *= 2.0; gam_n *= 0.5;  // descent lemma at x⁺: shrink this candidate's step and re-evaluate
+            prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
+          } else {
+            c_pend = false;
+            phi_n = psi_n + pTp_n / (2.0 * gam_n) + gTp_n;
+            double ls_cond = phi_n - (phi - sigma);
+            // NaN-safe: a non-finite phi+ is a failed trial (keeps back-tracking to the prox step)
+            c_acc = c_fb || (ls_cond <= (1.0 + fabs(phi)) * sp.ls_tol);
+          }
+        }
+        c_rq = false;
+        const unsigned pm = (__ballot_sync(tmask, c_valid && c_pend) & tmask) >> tbase;
+        const unsigned am = (__ballot_sync(tmask, c_valid && !c_pend && c_acc) & tmask) >> tbase;
+        const int first_acc = am ? __ffs(am) - 1 : G;
+        const unsigned below = (1u << first_acc) - 1u;  // first_acc <= G <= 8
+        if (pm & below) {  // an earlier candidate is still shrinking its step: it is decided first
+          if (c_valid && c_pend && l < first_acc) { evp = WL(M.XH(nb), l); want = 1; c_rq = true; }
           break;
         }
-        double phi_n = psi_n + pTp_n / (2.0 * gam_n) + gTp_n;
-        double ls_cond = phi_n - (phi - sigma);
-        tau *= 0.5;
-        // NaN-safe: a non-finite phi+ is a failed trial (keeps back-tracking to the prox step)
-        if (!(ls_cond <= (1.0 + fabs(phi)) * sp.ls_tol) && tau >= sp.tau_min) { state = ST_LS_TRIAL; continue; }
-        // accept: L-BFGS update with s = x⁺ − x, y = ∇ψ⁺ − ∇ψ (Appendix A 3e)
+        if (first_acc == G) { ++lsb; state = ST_LS_REQ; continue; }  // all rejected: next batch of candidates
+        // accept candidate jw: L-BFGS update with s = x⁺ − x, y = ∇ψ⁺ − ∇ψ (Appendix A 3e)
+        const int jw = first_acc;
         {
-          Vec X = W(M.X(bank)), XN = W(M.X(nb)), G = W(M.G(bank)), GN = W(M.G(nb));
-          Vec S = W(M.LS + lb_idx * n), Y = W(M.LY + lb_idx * n);
+          Vec X = WL(M.X(cb), cl), XN = WL(M.X(nb), jw), Gc = WL(M.G(cb), cl), GN = WL(M.G(nb), jw);
           double sy = 0.0, ss = 0.0;
           bool same = true;
-          for (int i = 0; i < n; ++i) {
-            double xi = X(i), xni = XN(i);
-            double s = xni - xi, y = GN(i) - G(i);
-            S.set(i, s);
-            Y.set(i, y);
-            sy += s * y;
-            ss += s * s;
-            same = same && (xi == xni);
+          for (int j = 0; j < ne; ++j) {
+            int e = l + G * j;
+            if (e < n) {
+              double xi = X(e), xni = XN(e);
+              double s = xni - xi, y = GN(e) - Gc(e);
+              tv(T.LS + lb_idx * T.np, e) = s;
+              tv(T.LY + lb_idx * T.np, e) = y;
+              sy += s * y;
+              ss += s * s;
+              same = same && (xi == xni);
+            }
           }
+          sy = tsum(sy); ss = tsum(ss);
+          same = (__ballot_sync(tmask, !same) & tmask) == 0;
           const double tiny = 1.4916681462400413e-154;  // sqrt(DBL_MIN)
           if (isfinite(sy) && ss >= tiny && sy >= tiny) {
             if (++lb_idx == mem) { lb_idx = 0; lb_full = 1; }
           }
           if (no_prog > 0 || k % sp.max_no_progress == 0) no_prog = same ? no_prog + 1 : 0;
         }
-        bank = nb;
-        psi = psi_n; psi_hat = psi_hat_n; gTp = gTp_n; pTp = pTp_n; L = L_n; gam = gam_n; phi = phi_n;
+        psi = tbcast(psi_n, jw); psi_hat = tbcast(psi_hat_n, jw);
+        gTp = tbcast(gTp_n, jw); pTp = tbcast(pTp_n, jw);
+        L = tbcast(L_n, jw); gam = tbcast(gam_n, jw);
+        phi = tbcast(phi_n, jw);
+        cl = jw; cb = nb;
+        tsync();
         ++k;
         state = ST_ITER_TOP;
       } else if (state == ST_PANOC_EXIT) {
         inner_total += k;
-        Vec X = W(M.X(bank));
         if (pstatus == MPCB_STATUS_NOT_FINITE) {  // failed instances keep their warm start
-          Vec XB = W(M.XB);
-          for (int i = 0; i < n; ++i) a.U[b * n + i] = XB(i);
-          a.status[b] = MPCB_STATUS_NOT_FINITE;
-          a.iters[2 * b] = alm_i + 1; a.iters[2 * b + 1] = inner_total;
-          a.evals[2 * b] = n_val; a.evals[2 * b + 1] = n_grad;
-          a.psi[b] = ppsi; a.res[b] = peps;
+          finish_instance(MPCB_STATUS_NOT_FINITE, true);
           state = ST_IDLE;
           continue;
         }
-        Vec XH = W(M.XH(bank));
-        for (int i = 0; i < n; ++i) X.set(i, XH(i));  // return x̂_k
+        // return x̂_k: it becomes lane 0 / bank 0's x (the next PANOC run of the ALM loop starts there)
+        if (l == 0) {
+          Vec XH = WL(M.XH(cb), cl), X0 = WL(M.X(0), 0);
+          for (int i = 0; i < n; ++i) X0.set(i, XH(i));
+        }
+        cl = 0; cb = 0;
+        tsync();
         norm_e2 = 0.0;
-        if (d.bounded) { ep = M.X(bank); want = 3; state = ST_ALM_V; break; }
+        if (d.bounded) {
+          if (l == 0) { evp = WL(M.X(0), 0); want = 3; }
+          state = ST_ALM_V;
+          break;
+        }
         state = ST_ALM_UPDATE;
       } else if (state == ST_ALM_V) {
         // err_z = g(x̂) − Π_D(ζ), λ ← ŷ(x̂)
-        Vec STt = W(M.ST), SG = W(M.SIG), E2 = W(M.E2);
+        Vec STt = WL(M.ST, 0);
         norm_e2 = 0.0;
         for (int r = 0; r < m; ++r) {
           int i = r % NX;
           double y = STt(r);
           double yh, ez;
-          alm_row(y * y - d.g_off[i], a.lam[b * m + r], SG(r), d.D_lo[i], d.D_hi[i], &yh, &ez);
-          E2.set(r, ez);
+          alm_row(y * y - d.g_off[i], a.lam[b * m + r], TR(T.SIG, r), d.D_lo[i], d.D_hi[i], &yh, &ez);
+          TR(T.E2, r) = ez;
           norm_e2 = fmax(norm_e2, fabs(ez));
         }
-        for (int r = 0; r < m; ++r) {
-          int i = r % NX;
-          double y = STt(r);
-          double yh, ez;
-          alm_row(y * y - d.g_off[i], a.lam[b * m + r], SG(r), d.D_lo[i], d.D_hi[i], &yh, &ez);
-          a.lam[b * m + r] = yh;
+        tsync();  // every lane has read the old multipliers before lane 0 overwrites them
+        if (l == 0) {
+          for (int r = 0; r < m; ++r) {
+            int i = r % NX;
+            double y = STt(r);
+            double yh, ez;
+            alm_row(y * y - d.g_off[i], a.lam[b * m + r], TR(T.SIG, r), d.D_lo[i], d.D_hi[i], &yh, &ez);
+            a.lam[b * m + r] = yh;
+          }
         }
+        tsync();
         state = ST_ALM_UPDATE;
       } else /* ST_ALM_UPDATE */ {
         bool inner_conv = pstatus == MPCB_STATUS_CONVERGED;
@@ -368,23 +528,21 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         else if (alm_i + 1 == sp.alm_max_iter) fin = MPCB_STATUS_MAX_ITER;
         else if (!inner_conv && eps_tol <= sp.eps_target) fin = pstatus;
         if (fin) {
-          Vec X = W(M.X(bank));
-          for (int i = 0; i < n; ++i) a.U[b * n + i] = X(i);
-          a.status[b] = fin;
-          a.iters[2 * b] = alm_i + 1; a.iters[2 * b + 1] = inner_total;
-          a.evals[2 * b] = n_val; a.evals[2 * b + 1] = n_grad;
-          a.psi[b] = ppsi; a.res[b] = peps;
+          finish_instance(fin, false);
           state = ST_IDLE;
           continue;
         }
         if (d.bounded) {
-          Vec SG = W(M.SIG), E1 = W(M.E1), E2 = W(M.E2);
-          for (int r = 0; r < m; ++r) {
-            double e2 = E2(r);
-            if (norm_e2 > sp.delta_target && (alm_i == 0 || fabs(e2) > sp.theta * fabs(E1(r))))
-              SG.set(r, fmin(sp.Sigma_max, fmax(sp.Delta * fabs(e2) / norm_e2, 1.0) * SG(r)));
-            E1.set(r, e2);
+          tsync();
+          if (l == 0) {
+            for (int r = 0; r < m; ++r) {
+              double e2 = TR(T.E2, r);
+              if (norm_e2 > sp.delta_target && (alm_i == 0 || fabs(e2) > sp.theta * fabs(TR(T.E1, r))))
+                TR(T.SIG, r) = fmin(sp.Sigma_max, fmax(sp.Delta * fabs(e2) / norm_e2, 1.0) * TR(T.SIG, r));
+              TR(T.E1, r) = e2;
+            }
           }
+          tsync();
         }
         eps_tol = fmax(sp.rho * eps_tol, sp.eps_target);
         ++alm_i;
@@ -393,20 +551,22 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     }
     // ================= evaluation phase: the one convergent site ================================
     if (!__any_sync(0xffffffffu, want != 0)) break;
+    const bool anyg = __any_sync(0xffffffffu, want == 2);
     if (want) {
       RoadView r = road_view(a.ra, sroad, d.S, b);
       Extras ex{a.obs ? a.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? a.lam + b * m : nullptr,
-                d.bounded ? a.ws + (int64_t)M.SIG * ns + slot : nullptr, 1, ns};
+                d.bounded ? &TR(T.SIG, 0) : nullptr, 1, nt};
       double y0[NX];
 #pragma unroll
       for (int i = 0; i < NX; ++i) y0[i] = a.x0[b * NX + i];
-      Vec Uv = W(ep);
-      const Vec stv = want == 3 ? W(M.ST) : Vec{nullptr, 0};
-      if (__any_sync(__activemask(), want == 2)) val = eval_fm<MODEL, true>(d, v, r, ex, y0, Uv, scr, W(eg), want == 2, stv);
-      else val = eval_fm<MODEL, false>(d, v, r, ex, y0, Uv, scr, W(eg), false, stv);
+      const Vec scr = WL(M.SCR, l);
+      const Vec stv = want == 3 ? WL(M.ST, l) : Vec{nullptr, 0};
+      if (anyg) val = eval_fm<MODEL, true>(d, v, r, ex, y0, evp, scr, evg, want == 2, stv);
+      else val = eval_fm<MODEL, false>(d, v, r, ex, y0, evp, scr, evg, false, stv);
       if (want == 2) ++n_grad;
       else if (want == 1) ++n_val;
     }
+    __syncwarp();
   }
 }
 

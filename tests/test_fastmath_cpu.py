@@ -25,6 +25,9 @@ def fm():
     lib.fmh_sincos.argtypes = [dp, dp, dp, C.c_long]
     lib.fmh_atan.argtypes = [dp, dp, C.c_long]
     lib.fmh_sin.argtypes = [dp, dp, C.c_long]
+    lib.fmh_sincos_x2.argtypes = [dp, dp, dp, C.c_long]
+    lib.fmh_sin_x2.argtypes = [dp, dp, C.c_long]
+    lib.fmh_atan_x2.argtypes = [dp, dp, C.c_long, C.c_int]
     return lib
 
 
@@ -69,3 +72,25 @@ def test_atan_matches_libm(fm):
     n = np.array([np.nan])
     fm.fmh_atan(_ptr(n), _ptr(y), 1)
     assert np.isnan(y[0])
+
+
+def test_paired_branch_free_cores(fm):
+    """The *_x2 cores the model call uses on its fast path (ranges guaranteed by the caller)."""
+    rng = np.random.default_rng(2)
+    x = np.concatenate([rng.uniform(-8, 8, 200000), rng.uniform(-1e5, 1e5, 100000), np.array([0.0, -0.0, np.pi / 2, -np.pi])])
+    s, c, s1 = np.empty_like(x), np.empty_like(x), np.empty_like(x)
+    fm.fmh_sincos_x2(_ptr(x), _ptr(s), _ptr(c), x.size)
+    assert np.max(np.abs(s - np.sin(x))) < 3e-16 and np.max(np.abs(c - np.cos(x))) < 3e-16
+    fm.fmh_sin_x2(_ptr(x), _ptr(s1), x.size)
+    assert np.max(np.abs(s1 - np.sin(x))) < 3e-16
+    big = np.abs(np.sin(x)) > 0.1
+    assert _ulps(s1[big], np.sin(x[big])).max() <= 2.0
+    for small, lim in ((1, 0.5), (0, 1.0)):
+        a = np.concatenate([rng.uniform(-lim, lim, 300000), np.array([0.0, -0.0, lim, -lim, 1e-200, -1e-9])])
+        y = np.empty_like(a)
+        fm.fmh_atan_x2(_ptr(a), _ptr(y), a.size, small)
+        ref = np.arctan(a)
+        ok = ref != 0
+        assert _ulps(y[ok], ref[ok]).max() <= 2.0
+        nz = a != 0  # the branch-free form returns +0 for -0 (irrelevant to the model)
+        assert np.all(np.signbit(y[nz]) == np.signbit(a[nz]))

@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(128) k_chain(double* out, int iters, long long
   __syncthreads();
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   StageU su;
+  v.trig_ok = 1;
   make_stage_u<MPCB_MODEL_PACEJKA6>(su, 0.6, 0.05 + 1e-4 * (t & 31), v, GRAD);
   double p[2] = {0, 0}, q[4] = {0.1 + 1e-3 * (t & 7), 1.0, 0.01, 0.1};
   double tp[5][2], tq[5][4];
