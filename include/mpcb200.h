@@ -194,6 +194,11 @@ int mpcb_fp64_peak(double* tflops_out, double* ms_out);
  * [0] DFMA [1] div [2] sqrt [3] sincos [4] atan [5] atan2 [6] sin [7] one Pacejka model call. */
 int mpcb_latency_probe(double* cycles8);
 
+/* Diagnostic, enabled by MPCB_DEBUG_TIMERS=1 in the environment at mpcb_create: per-warp
+ * [evaluation cycles, transition cycles, rounds, gradient rounds] of the last mpcb_solve.  Returns the number of
+ * warps written (<= max_warps). */
+int64_t mpcb_debug_timers(MpcHandle* h, long long* out4, int64_t max_warps);
+
 /* Number of kernels launched through this handle since creation (bench.py's gpu_launches). */
 int64_t mpcb_launch_count(MpcHandle* h);
 

@@ -56,6 +56,7 @@ SIGNATURES = {
     "mpcb_default_desc": (None, [C.POINTER(MpcProblemDesc), C.c_int32, C.c_int32, C.c_int32]),
     "mpcb_default_solver_params": (None, [C.POINTER(MpcSolverParams), C.c_int32]),
     "mpcb_default_vehicle_params": (None, [C.POINTER(C.c_double)]),
+    "mpcb_debug_timers": (C.c_int64, [C.c_void_p, C.POINTER(C.c_longlong), C.c_int64]),
     "mpcb_create": (C.c_int, [C.POINTER(MpcProblemDesc), C.POINTER(C.c_void_p)]),
     "mpcb_destroy": (None, [C.c_void_p]),
     "mpcb_last_error": (C.c_char_p, [C.c_void_p]),

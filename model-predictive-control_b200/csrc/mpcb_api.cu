@@ -24,6 +24,8 @@ struct MpcHandle {
   double* road_t = nullptr; size_t road_t_cap = 0;     // transposed per-instance roads [2S, ld]
   double* ws = nullptr; size_t ws_cap = 0;             // solver / value_grad workspace
   double* wst = nullptr; size_t wst_cap = 0;           // per-tile solver workspace
+  long long* dbg = nullptr; size_t dbg_cap = 0; int64_t dbg_warps = 0; int debug_timers = 0;  // MPCB_DEBUG_TIMERS=1
+  int warps_per_sm = 8;                                // MPCB_WARPS_PER_SM env (experiments)
   int tile_override = 0;                               // MPCB_TILE env: force the lanes-per-instance width
   int last_tile = 0;
   unsigned long long* queue = nullptr;
@@ -194,6 +196,8 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
   if (cudaMalloc((void**)&h->queue, sizeof(unsigned long long)) != cudaSuccess) { delete h; return MPCB_E_CUDA; }
   if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
   if (cudaEventCreateWithFlags(&h->last_ev, cudaEventDisableTiming) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
+  if (const char* e = std::getenv("MPCB_DEBUG_TIMERS")) h->debug_timers = std::atoi(e);
+  if (const char* e = std::getenv("MPCB_WARPS_PER_SM")) { int w = std::atoi(e); if (w >= 1 && w <= 8) h->warps_per_sm = w; }
   if (const char* e = std::getenv("MPCB_TILE")) {
     int g = std::atoi(e);
     if (g == 1 || g == 2 || g == 4 || g == 8) h->tile_override = g;
@@ -204,7 +208,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
 
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
-  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
+  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
   if (h->pin) cudaFreeHost(h->pin);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   if (h->last_ev) cudaEventDestroy(h->last_ev);
@@ -346,9 +350,9 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   // Tile width: the solve is latency-bound, so spare lanes are spent on speculative line-search
   // candidates (mpcb_solve.cuh).  255-register lanes: 8 warps per SM resident.
   const int block = 64;
-  const int64_t lane_cap = (int64_t)h->num_sms * 8 * 32;
+  const int64_t lane_cap = (int64_t)h->num_sms * h->warps_per_sm * 32;
   int G = 1;
-  for (int g : {8, 4, 2}) if (B * g <= lane_cap) { G = g; break; }
+  for (int g : {8, 4, 2}) if (B * g <= (int64_t)h->num_sms * 8 * 32) { G = g; break; }
   if (h->tile_override > 0) G = h->tile_override;
   int64_t tiles_wanted = B;
   int64_t blocks = (tiles_wanted * G + block - 1) / block;
@@ -367,6 +371,13 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   a.B = B; a.x0 = x0; a.p = p; a.obs = obs; a.lb = lb; a.ub = ub; a.ra = ra; a.U = U; a.lam = lambda;
   a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res;
   a.ws = h->ws; a.wst = h->wst; a.ns = ns; a.nt = nt; a.queue = h->queue;
+  a.dbg = nullptr;
+  if (h->debug_timers) {
+    if ((rc = grow(h, &h->dbg, &h->dbg_cap, (size_t)(ns / 32) * 4 * sizeof(long long), st))) return rc;
+    CK(cudaMemsetAsync(h->dbg, 0, (size_t)(ns / 32) * 4 * sizeof(long long), st));
+    a.dbg = h->dbg;
+    h->dbg_warps = ns / 32;
+  }
 #define MPCB_LAUNCH_SOLVE(MODEL, GG)                                                           \
   do {                                                                                         \
     if ((rc = set_smem(h, k_solve<MODEL, GG>, smem))) return rc;                               \
@@ -467,6 +478,16 @@ int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const do
   h->h2d_bytes = (int64_t)in_end;
   h->d2h_bytes = (int64_t)(total - o_U);
   return MPCB_OK;
+}
+
+/* Diagnostic (MPCB_DEBUG_TIMERS=1): per-warp [eval cycles, transition cycles, rounds, gradient rounds] of the
+ * last mpcb_solve; returns the number of warps copied (<= max_warps), synchronises the device. */
+int64_t mpcb_debug_timers(MpcHandle* h, long long* out, int64_t max_warps) {
+  if (!h || !h->dbg || !out) return 0;
+  int64_t nw = h->dbg_warps < max_warps ? h->dbg_warps : max_warps;
+  if (cudaDeviceSynchronize() != cudaSuccess) return 0;
+  if (cudaMemcpy(out, h->dbg, (size_t)nw * 4 * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return 0;
+  return nw;
 }
 
 void mpcb_last_transfer_bytes(MpcHandle* h, int64_t* h2d, int64_t* d2h) {

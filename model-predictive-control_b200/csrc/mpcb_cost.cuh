@@ -6,15 +6,27 @@
 
 namespace mpcb {
 
-// A road as the kernels see it: x_i = xy[i*stride*2 .. ] is avoided; instead two strided views.
-//   shared-memory road: interleaved (x,y) pairs, rx = base, ry = base+1, stride 2
-//   SoA scratch road  : rx = roadT + b, ry = roadT + S*ld + b, stride ld
+// A road as the kernels see it.
+//   shared-memory road (table modes): interleaved (x, y) pairs at shared address sbase + 16 i, read with
+//     one explicit ld.shared.v2.f64 (through a generic pointer the compiler emitted LD.E + spilled
+//     address arithmetic in the scan loop);
+//   SoA scratch road (per-instance modes): rx = roadT + b, ry = roadT + S*ld + b, stride ld.
 struct RoadView {
   const double* rx;
   const double* ry;
   int64_t stride;
-  MPCB_DEV double x(int i) const { return rx[(int64_t)i * stride]; }
-  MPCB_DEV double y(int i) const { return ry[(int64_t)i * stride]; }
+  unsigned sbase;
+  int smem;
+  MPCB_DEV void xy(int i, double& x, double& y) const {
+    if (smem) {
+      asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(sbase + 16u * (unsigned)i));
+    } else {
+      x = rx[(int64_t)i * stride];
+      y = ry[(int64_t)i * stride];
+    }
+  }
+  MPCB_DEV double x(int i) const { double a, b; xy(i, a, b); return a; }
+  MPCB_DEV double y(int i) const { double a, b; xy(i, a, b); return b; }
 };
 
 #define MPCB_PI 3.141592653589793238462643383279502884
@@ -27,28 +39,100 @@ MPCB_DEV double wrap_to_pi(double a) {
   return m - MPCB_PI;
 }
 
-// car_dynamics.py:174-192: the reference compares sqrt'ed distances with a strict '<' over
-// i = 1..S-2 starting from vertex 0.  sqrt is monotone, so the scan runs on squared distances
-// (rounded exactly like diff**2 summed: two products, one add, no FMA) and only falls back to the
-// sqrt comparison when two candidates are within a few ulp — same winner, bit for bit.
-MPCB_DEV int nearest_scan(const RoadView& r, int S, double px, double py) {
-  double dx = r.x(0) - px, dy = r.y(0) - py;
-  double m2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-  double m2lo = m2 * (1.0 - 1.8e-15);
+MPCB_DEV double d2_of(double x, double y, double px, double py) {
+  double dx = x - px, dy = y - py;
+  return __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));  // rounded like diff**2 summed (no FMA)
+}
+MPCB_DEV double road_d2(const RoadView& r, int i, double px, double py) {
+  double x, y;
+  r.xy(i, x, y);
+  return d2_of(x, y, px, py);
+}
+
+// Exact restatement of car_dynamics.py:174-192 (sqrt'ed distances, strict '<', i = 1..S-2 from vertex 0):
+// only runs when two vertices are within rounding of the minimum.
+__device__ __noinline__ int nearest_scan_exact(RoadView r, int S, double px, double py) {
+  double m = sqrt(road_d2(r, 0, px, py));
   int best = 0;
-#pragma unroll 4
   for (int i = 1; i < S - 1; ++i) {
-    dx = r.x(i) - px;
-    dy = r.y(i) - py;
-    double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-    if (d2 < m2) {
-      if (d2 < m2lo || sqrt(d2) < sqrt(m2)) {
-        m2 = d2;
-        m2lo = m2 * (1.0 - 1.8e-15);
-        best = i;
-      }
-    }
+    double di = sqrt(road_d2(r, i, px, py));
+    if (di < m) { m = di; best = i; }
   }
+  return best;
+}
+
+// car_dynamics.py:174-192.  The reference compares sqrt'ed distances with a strict '<', so its answer is
+// the lowest index attaining the minimal sqrt.  sqrt is monotone: that is the first index of the minimal
+// squared distance unless another vertex lies within rounding of it.  The scan therefore tracks the
+// minimum, its first index and the second-smallest entry with selects only (two independent chains
+// over the two halves of the range, no branches, no sqrt), and falls back to the exact scan when the
+// runner-up is within 4.5e-16 of the minimum — same winner, bit for bit.  Not inlined: its own
+// register allocation (inside the gradient evaluation it was reloading spilled addresses per vertex).
+struct ScanLoadShared {
+  unsigned a;
+  MPCB_DEV void at(int i, double& x, double& y) const {
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(a + 16u * (unsigned)i));
+  }
+};
+struct ScanLoadStrided {
+  const double* rx;
+  const double* ry;
+  int64_t stride;
+  MPCB_DEV void at(int i, double& x, double& y) const { x = rx[(int64_t)i * stride]; y = ry[(int64_t)i * stride]; }
+};
+template <class LD>
+MPCB_DEV bool nearest_scan_core(const LD& ld, int S, double px, double py, int* best_out) {
+  const int n = S - 1;         // candidates 0 .. S-2
+  const int h = (n + 1) >> 1;  // chain A: [0, h), chain B: [h, n)
+  const double inf = __longlong_as_double(0x7ff0000000000000LL);
+  double x, y;
+  ld.at(0, x, y);
+  double ma = d2_of(x, y, px, py), sa = inf, mb = inf, sb = inf;
+  int ba = 0, bb = n;
+#pragma unroll 4
+  for (int i = 1; i < h; ++i) {
+    const int j = h + i - 1;  // < n for every i < h
+    double xa, ya, xb, yb;
+    ld.at(i, xa, ya);
+    ld.at(j, xb, yb);
+    const double da = d2_of(xa, ya, px, py), db = d2_of(xb, yb, px, py);
+    const bool la = da < ma, lb = db < mb;
+    sa = la ? ma : fmin(sa, da);
+    sb = lb ? mb : fmin(sb, db);
+    ba = la ? i : ba;
+    bb = lb ? j : bb;
+    ma = la ? da : ma;
+    mb = lb ? db : mb;
+  }
+  if (2 * h - 1 < n) {  // n even: chain B holds one more element than the loop visited
+    const int j = 2 * h - 1;
+    ld.at(j, x, y);
+    const double db = d2_of(x, y, px, py);
+    const bool lb = db < mb;
+    sb = lb ? mb : fmin(sb, db);
+    bb = lb ? j : bb;
+    mb = lb ? db : mb;
+  }
+  const bool lb = mb < ma;  // merge: the lower-index chain wins ties
+  const double m = lb ? mb : ma;
+  const double second = fmin(fmin(sa, sb), lb ? ma : mb);
+  *best_out = lb ? bb : ba;
+  return second > m * (1.0 + 4.5e-16);  // false: near-tie (or NaN) -> the exact rule decides
+}
+__device__ __noinline__ int nearest_scan_shared(unsigned sbase, int S, double px, double py) {
+  int best;
+  if (nearest_scan_core(ScanLoadShared{sbase}, S, px, py, &best)) return best;
+  return -1;
+}
+__device__ __noinline__ int nearest_scan_strided(const double* rx, const double* ry, int64_t stride, int S, double px,
+                                                 double py) {
+  int best;
+  if (nearest_scan_core(ScanLoadStrided{rx, ry, stride}, S, px, py, &best)) return best;
+  return -1;
+}
+MPCB_DEV int nearest_scan(const RoadView& r, int S, double px, double py) {
+  int best = r.smem ? nearest_scan_shared(r.sbase, S, px, py) : nearest_scan_strided(r.rx, r.ry, r.stride, S, px, py);
+  if (best < 0) best = nearest_scan_exact(r, S, px, py);
   return best;
 }
 
@@ -76,10 +160,12 @@ struct RoadGeom {  // the three vertices the errors are built from, as differenc
 MPCB_DEV void road_geom(const RoadView& r, int idx, RoadGeom& g) {
   int ip = idx > 0 ? idx - 1 : 0;  // vertex 0 wins: previous = vertex 0 (car_dynamics.py:183)
   int in = idx + 1;
-  g.nx = r.x(idx); g.ny = r.y(idx);
-  g.ax = r.x(ip); g.ay = r.y(ip);
+  double qx, qy;
+  r.xy(idx, g.nx, g.ny);
+  r.xy(ip, g.ax, g.ay);
+  r.xy(in, qx, qy);
   g.wx = g.nx - g.ax; g.wy = g.ny - g.ay;
-  g.w2x = r.x(in) - g.nx; g.w2y = r.y(in) - g.ny;
+  g.w2x = qx - g.nx; g.w2y = qy - g.ny;
 }
 
 // car_dynamics.py:194-228: cte, heading error, positional error (raw cross products).

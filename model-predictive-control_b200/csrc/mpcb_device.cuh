@@ -43,6 +43,19 @@ MPCB_DEV void load_vehicle(VehP* v, const double* __restrict__ p, const KDesc& d
   v->trig_ok = fabs(p[12]) < 8.0e4 && fabs(p[15]) < 8.0e4;
 }
 
+// Problem description and vehicle constants of the running kernel, at file scope in shared memory so the
+// non-inlined evaluation function (mpcb_fwd.cuh) reads them with LDS instead of through generic pointers.
+static __shared__ VehP s_veh;
+static __shared__ KDesc s_desc;
+// Called by every thread of a kernel before it evaluates anything (ends with a block barrier).
+MPCB_DEV void stage_problem(const KDesc& d, const double* __restrict__ p) {
+  if (threadIdx.x == 0) {
+    s_desc = d;
+    load_vehicle(&s_veh, p, d);
+  }
+  __syncthreads();
+}
+
 // Stage input with its hoisted trigonometry (delta is constant over the 16 model calls of a stage).
 struct StageU {
   double d, dl, sdl, cdl;

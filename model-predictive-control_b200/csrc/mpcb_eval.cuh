@@ -41,13 +41,15 @@ MPCB_DEV RoadView road_view(const RoadArg& ra, const double* sroad, int S, int64
   RoadView r;
   if (ra.in_smem) {
     int ridx = ra.road_idx ? ra.road_idx[b] : 0;
-    r.rx = sroad + (int64_t)ridx * 2 * S;
-    r.ry = r.rx + 1;
-    r.stride = 2;
+    r.rx = nullptr; r.ry = nullptr; r.stride = 0;
+    r.sbase = (unsigned)__cvta_generic_to_shared(sroad + (int64_t)ridx * 2 * S);
+    r.smem = 1;
   } else {
     r.rx = ra.road + b;
     r.ry = ra.road + (int64_t)S * ra.ld + b;
     r.stride = ra.ld;
+    r.sbase = 0;
+    r.smem = 0;
   }
   return r;
 }

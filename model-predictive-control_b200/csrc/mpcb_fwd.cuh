@@ -259,38 +259,70 @@ MPCB_DEV void rk4_fm(double* p, double* q, double (*tp)[2], double (*tq)[Fm<MODE
 template <int MODEL>
 __host__ __device__ constexpr int fm_stage_doubles() { return Fm<MODEL>::NX * Fm<MODEL>::ND + 2 + Fm<MODEL>::NX; }
 
-// psi (returned) and, with GRAD and store, grad psi into `grad`.  states/idx_out (p may be null)
-// receive the stage-end states and nearest-vertex indices.
+// One horizon stage: n_sub RK4 elements from pq (in/out, NX doubles in local memory) under input (ud, udl);
+// with GRAD and store the stage Jacobian T and (dx, dy) go straight to the scratch at offset o.  Not
+// inlined: the 30 tangent components + RK4 temporaries need the whole register file to themselves
+// (242 registers, no spills, tools/ubench_model.cu); inlined into the evaluation loop they spilled.
 template <int MODEL, bool GRAD>
-MPCB_DEV double eval_fm(const KDesc& d, const VehP& v, const RoadView& r, const Extras& ex, const double* x0,
-                        const Vec& U, const Vec& scr, const Vec& grad, bool store, const Vec& states = Vec{nullptr, 0},
-                        const IVec& idx_out = IVec{nullptr, 0}) {
+__device__ __noinline__ void stage_fm(double* pq, double ud, double udl, Vec scr, int o, bool store) {
   using M = Fm<MODEL>;
-  constexpr int NX = M::NX, NQ = M::NQ, ND = M::ND, K = fm_stage_doubles<MODEL>();
-  double p[2] = {x0[0], x0[1]}, q[NQ];
+  constexpr int NX = M::NX, NQ = M::NQ, ND = M::ND;
+  const VehP& v = s_veh;
+  StageU su;
+  make_stage_u<MODEL>(su, ud, udl, v, GRAD);
+  double p[2] = {pq[0], pq[1]}, q[NQ];
 #pragma unroll
-  for (int i = 0; i < NQ; ++i) q[i] = x0[2 + i];
+  for (int i = 0; i < NQ; ++i) q[i] = pq[2 + i];
+  double tp[GRAD ? ND : 1][2], tq[GRAD ? ND : 1][NQ];
+  if (GRAD) {
+    ForDir<0, ND>::run([&](auto J) {
+      constexpr int j = decltype(J)::value;
+      tp[j][0] = 0.0; tp[j][1] = 0.0;
+      M::template seed<j>(tq[j]);
+    });
+  }
+  const double px0 = p[0], py0 = p[1];
+  const int n_sub = s_desc.n_sub;
+  const double h = s_desc.h;
+#pragma unroll 1
+  for (int e = 0; e < n_sub; ++e) rk4_fm<MODEL, GRAD>(p, q, tp, tq, su, v, h);
+  pq[0] = p[0]; pq[1] = p[1];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) pq[2 + i] = q[i];
+  if (GRAD && store) {
+#pragma unroll
+    for (int j = 0; j < ND; ++j) {
+      scr.set(o + j * NX, tp[j][0]);
+      scr.set(o + j * NX + 1, tp[j][1]);
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) scr.set(o + j * NX + 2 + i, tq[j][i]);
+    }
+    scr.set(o + NX * ND, p[0] - px0);
+    scr.set(o + NX * ND + 1, p[1] - py0);
+  }
+}
+
+// Deliberately NOT inlined: the evaluation gets its own register allocation (the solver's state machine
+// around it kept ~60 values live and pushed the scan and model loops into local-memory reloads), and
+// the kernels stay small enough for the instruction cache.  Reads the problem from s_desc / s_veh
+// (stage_problem()).
+template <int MODEL, bool GRAD>
+__device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, Vec U, Vec scr, Vec grad, bool store,
+                                       Vec states = Vec{nullptr, 0}, IVec idx_out = IVec{nullptr, 0}) {
+  const KDesc& d = s_desc;
+  const VehP& v = s_veh;
+  using M = Fm<MODEL>;
+  constexpr int NX = M::NX, ND = M::ND, K = fm_stage_doubles<MODEL>();
+  double y[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) y[i] = x0[i];
   double cost = 0.0;
 #pragma unroll 1
   for (int n = 0; n < d.N; ++n) {
     const double ud = U(2 * n), udl = U(2 * n + 1);
-    StageU su;
-    make_stage_u<MODEL>(su, ud, udl, v, GRAD);
-    double tp[GRAD ? ND : 1][2], tq[GRAD ? ND : 1][NQ];
-    if (GRAD) {
-      ForDir<0, ND>::run([&](auto J) {
-        constexpr int j = decltype(J)::value;
-        tp[j][0] = 0.0; tp[j][1] = 0.0;
-        M::template seed<j>(tq[j]);
-      });
-    }
-    const double px0 = p[0], py0 = p[1];
-#pragma unroll 1
-    for (int e = 0; e < d.n_sub; ++e) rk4_fm<MODEL, GRAD>(p, q, tp, tq, su, v, d.h);
-    double y[NX], gy[NX], gu[2];
-    y[0] = p[0]; y[1] = p[1];
-#pragma unroll
-    for (int i = 0; i < NQ; ++i) y[2 + i] = q[i];
+    const int o = n * K;
+    stage_fm<MODEL, GRAD>(y, ud, udl, scr, o, store);
+    double gy[NX], gu[2];
     int idx;
     cost += stage_cost<MODEL, GRAD, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
     if (states.p) {
@@ -299,16 +331,6 @@ MPCB_DEV double eval_fm(const KDesc& d, const VehP& v, const RoadView& r, const 
     }
     if (idx_out.p) idx_out.set(n, idx);
     if (GRAD && store) {
-      const int o = n * K;
-#pragma unroll
-      for (int j = 0; j < ND; ++j) {
-        scr.set(o + j * NX, tp[j][0]);
-        scr.set(o + j * NX + 1, tp[j][1]);
-#pragma unroll
-        for (int i = 0; i < NQ; ++i) scr.set(o + j * NX + 2 + i, tq[j][i]);
-      }
-      scr.set(o + NX * ND, p[0] - px0);
-      scr.set(o + NX * ND + 1, p[1] - py0);
 #pragma unroll
       for (int i = 0; i < NX; ++i) scr.set(o + NX * ND + 2 + i, gy[i]);
     }

@@ -34,9 +34,9 @@ template <int MODEL>
 __global__ void k_plant_step(KDesc d, int64_t B, const double* __restrict__ x, const double* __restrict__ u,
                              const double* __restrict__ p, double* __restrict__ out) {
   constexpr int NX = ModelTraits<MODEL>::NX;
-  __shared__ VehP v;
-  if (threadIdx.x == 0) load_vehicle(&v, p, d);
-  __syncthreads();
+  fm_load_smem();
+  stage_problem(d, p);
+  const VehP& v = s_veh;
   int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   double pq[NX];
@@ -60,7 +60,7 @@ __global__ void k_road_errors(KDesc d, int64_t B, const double* __restrict__ pos
   const double* base = road;
   if (d.road_mode == MPCB_ROAD_TABLE) base = road + (int64_t)(road_idx ? road_idx[b] : 0) * 2 * S;
   else if (d.road_mode == MPCB_ROAD_PER_INSTANCE) base = road + b * 2 * S;
-  RoadView r{base, base + S, 1};
+  RoadView r{base, base + S, 1, 0u, 0};
   double px = pos[2 * b], py = pos[2 * b + 1], phi = heading[b];
   double cte, he, pe;
   int idx;
@@ -135,10 +135,9 @@ k_rollout(KDesc d, int64_t B, const double* __restrict__ x0, const double* __res
           int32_t* idx_out, double* cost_out) {
   constexpr int NX = ModelTraits<MODEL>::NX;
   extern __shared__ double sroad[];
-  __shared__ VehP v;
-  if (threadIdx.x == 0) load_vehicle(&v, p, d);
+  fm_load_smem();
   if (ra.in_smem) stage_roads(sroad, ra.road, ra.R, d.S);
-  __syncthreads();
+  stage_problem(d, p);
   int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   RoadView r = road_view(ra, sroad, d.S, b);
@@ -148,7 +147,7 @@ k_rollout(KDesc d, int64_t B, const double* __restrict__ x0, const double* __res
   double y0[NX];
 #pragma unroll
   for (int i = 0; i < NX; ++i) y0[i] = x0[b * NX + i];
-  double cost = eval_fm<MODEL, false>(d, v, r, ex, y0, Uv, Vec{nullptr, 0}, Vec{nullptr, 0}, false,
+  double cost = eval_fm<MODEL, false>(r, ex, y0, Uv, Vec{nullptr, 0}, Vec{nullptr, 0}, false,
                                       Vec{states_out ? states_out + b * d.N * NX : nullptr, 1},
                                       IVec{idx_out ? idx_out + b * d.N : nullptr, 1});
   if (cost_out) cost_out[b] = cost;
@@ -164,10 +163,9 @@ k_value_grad(KDesc d, int64_t B, const double* __restrict__ x0, const double* __
              double* __restrict__ grad_out, double* scratch, int64_t ns) {
   constexpr int NX = ModelTraits<MODEL>::NX;
   extern __shared__ double sroad[];
-  __shared__ VehP v;
-  if (threadIdx.x == 0) load_vehicle(&v, p, d);
+  fm_load_smem();
   if (ra.in_smem) stage_roads(sroad, ra.road, ra.R, d.S);
-  __syncthreads();
+  stage_problem(d, p);
   int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const Vec scr{scratch + slot, ns};
   for (int64_t b = slot; b < B; b += ns) {
@@ -179,7 +177,7 @@ k_value_grad(KDesc d, int64_t B, const double* __restrict__ x0, const double* __
     for (int i = 0; i < NX; ++i) y0[i] = x0[b * NX + i];
     Vec Uv{const_cast<double*>(U) + b * d.n, 1};
     Vec Gv{grad_out + b * d.n, 1};
-    cost_out[b] = eval_fm<MODEL, true>(d, v, r, ex, y0, Uv, scr, Gv, true);
+    cost_out[b] = eval_fm<MODEL, true>(r, ex, y0, Uv, scr, Gv, true);
   }
 }
 

@@ -45,6 +45,7 @@ struct SolveArgs {
   double* wst;   // per-tile data   [TileMap.total, nt] (tile-vector region first, plain rows after)
   int64_t ns, nt;
   unsigned long long* queue;
+  long long* dbg;  // optional [warps, 4]: cycles in evaluation / transition phases, rounds, gradient rounds
 };
 
 enum SolveState {
@@ -81,15 +82,13 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   constexpr int NX = Fm<MODEL>::NX;
   constexpr int K = fm_stage_doubles<MODEL>();
   extern __shared__ double smem[];
-  __shared__ VehP v;
   const int n = d.n, m = d.m, mem = sp.lbfgs_mem;
   double* sroad = smem;
   double* sbox = smem + (a.ra.in_smem ? a.ra.R * d.S * 2 : 0);  // lb[n], ub[n]
   fm_load_smem();
-  if (threadIdx.x == 0) load_vehicle(&v, a.p, d);
   if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
   for (int i = threadIdx.x; i < n; i += blockDim.x) { sbox[i] = a.lb[i]; sbox[n + i] = a.ub[i]; }
-  __syncthreads();
+  stage_problem(d, a.p);
   const double* lbv = sbox;
   const double* ubv = sbox + n;
 
@@ -219,6 +218,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     n_val = 0; n_grad = 0;
   };
 
+  long long t_eval = 0, t_trans = 0, n_rounds = 0, n_grounds = 0, t_mark = clock64();
   for (;;) {
     // ================= transition phase: run the tile's state machine up to its next evaluation ====
     want = 0;
@@ -552,6 +552,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     // ================= evaluation phase: the one convergent site ================================
     if (!__any_sync(0xffffffffu, want != 0)) break;
     const bool anyg = __any_sync(0xffffffffu, want == 2);
+    { long long t = clock64(); t_trans += t - t_mark; t_mark = t; }
     if (want) {
       RoadView r = road_view(a.ra, sroad, d.S, b);
       Extras ex{a.obs ? a.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? a.lam + b * m : nullptr,
@@ -561,12 +562,17 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       for (int i = 0; i < NX; ++i) y0[i] = a.x0[b * NX + i];
       const Vec scr = WL(M.SCR, l);
       const Vec stv = want == 3 ? WL(M.ST, l) : Vec{nullptr, 0};
-      if (anyg) val = eval_fm<MODEL, true>(d, v, r, ex, y0, evp, scr, evg, want == 2, stv);
-      else val = eval_fm<MODEL, false>(d, v, r, ex, y0, evp, scr, evg, false, stv);
+      if (anyg) val = eval_fm<MODEL, true>(r, ex, y0, evp, scr, evg, want == 2, stv);
+      else val = eval_fm<MODEL, false>(r, ex, y0, evp, scr, evg, false, stv);
       if (want == 2) ++n_grad;
       else if (want == 1) ++n_val;
     }
     __syncwarp();
+    { long long t = clock64(); t_eval += t - t_mark; t_mark = t; ++n_rounds; n_grounds += anyg; }
+  }
+  if (a.dbg && lane == 0) {
+    long long* o = a.dbg + 4 * (slot >> 5);
+    o[0] = t_eval; o[1] = t_trans; o[2] = n_rounds; o[3] = n_grounds;
   }
 }
 

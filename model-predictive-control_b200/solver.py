@@ -82,6 +82,10 @@ class BatchedMpc:
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     def _t(self, x, shape=None, dtype=torch.float64):
+        # numpy / python inputs are uploaded (the reference-facing convenience); a torch tensor is taken as is:
+        # the wrong device or dtype is a loud error, never a silent conversion or a CPU path
+        if isinstance(x, torch.Tensor) and (x.device != self.device or x.dtype != dtype):
+            raise TypeError(f"expected a {dtype} tensor on {self.device}, got {x.dtype} on {x.device}")
         t = torch.as_tensor(x, dtype=dtype, device=self.device).contiguous()
         if shape is not None:
             t = t.reshape(shape)

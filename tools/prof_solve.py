@@ -28,6 +28,17 @@ def main():
         print(f"solve {i}: {dt * 1e3:.1f} ms, {B / dt:.0f} solves/s, converged {(st.status == 1).float().mean().item():.4f}, "
               f"inner mean {st.inner_iterations.double().mean().item():.1f} max {st.inner_iterations.max().item()}, "
               f"evals value {st.evals_value.double().mean().item():.1f} grad {st.evals_grad.double().mean().item():.1f}")
+    if os.environ.get("MPCB_DEBUG_TIMERS"):
+        import ctypes as C
+        import numpy as np
+        buf = (C.c_longlong * (4 * 4096))()
+        nw = mpcb200._ffi.lib().mpcb_debug_timers(prob._h, buf, 4096)
+        t = np.frombuffer(buf, dtype=np.int64)[:4 * nw].reshape(nw, 4).astype(float)
+        tot = t[:, 0] + t[:, 1]
+        i = int(np.argmax(tot))
+        print(f"timers over {nw} warps: eval share {t[:, 0].sum() / tot.sum():.3f}, mean rounds {t[:, 2].mean():.0f} (grad {t[:, 3].mean():.0f}), "
+              f"cycles/round eval {t[:, 0].sum() / t[:, 2].sum():.0f} transition {t[:, 1].sum() / t[:, 2].sum():.0f}; "
+              f"slowest warp: {tot[i] / 1.965e6:.1f} ms, rounds {t[i, 2]:.0f}, eval/round {t[i, 0] / t[i, 2]:.0f}, trans/round {t[i, 1] / t[i, 2]:.0f}")
 
 
 if __name__ == "__main__":
