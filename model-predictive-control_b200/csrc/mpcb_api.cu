@@ -77,6 +77,7 @@ KDesc make_kdesc(const MpcProblemDesc& d) {
   k.lane_a = d.lane_a; k.lane_y_t = d.lane_y_t; k.lane_b = d.lane_b; k.lane_y_br = d.lane_y_br; k.lane_y_bl = d.lane_y_bl;
   k.obs_Af = d.obs_Af; k.obs_b = d.obs_b; k.obs_sx = d.obs_sigma_x; k.obs_sy = d.obs_sigma_y; k.obs_adiv = d.obs_alpha_div;
   k.bounded = 0;
+  k.debug = 0;
   if (d.flags & MPCB_FLAG_BOUNDED_D)
     for (int i = 0; i < k.nx; ++i)
       if (!std::isinf(d.D_lower[i]) || !std::isinf(d.D_upper[i])) k.bounded = 1;
@@ -372,7 +373,10 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res;
   a.ws = h->ws; a.wst = h->wst; a.ns = ns; a.nt = nt; a.queue = h->queue;
   a.dbg = nullptr;
+  h->kd.debug = h->debug_timers;
   if (h->debug_timers) {
+    unsigned long long z[2] = {0, 0};
+    CK(cudaMemcpyToSymbolAsync(g_dbg_calls, z, sizeof(z), 0, cudaMemcpyHostToDevice, st));
     if ((rc = grow(h, &h->dbg, &h->dbg_cap, (size_t)(ns / 32) * 4 * sizeof(long long), st))) return rc;
     CK(cudaMemsetAsync(h->dbg, 0, (size_t)(ns / 32) * 4 * sizeof(long long), st));
     a.dbg = h->dbg;
@@ -487,6 +491,10 @@ int64_t mpcb_debug_timers(MpcHandle* h, long long* out, int64_t max_warps) {
   int64_t nw = h->dbg_warps < max_warps ? h->dbg_warps : max_warps;
   if (cudaDeviceSynchronize() != cudaSuccess) return 0;
   if (cudaMemcpy(out, h->dbg, (size_t)nw * 4 * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return 0;
+  unsigned long long c[2] = {0, 0};
+  if (cudaMemcpyFromSymbol(c, g_dbg_calls, sizeof(c)) == cudaSuccess)
+    std::fprintf(stderr, "[mpcb debug] model calls: fast path %llu, general path %llu (%.2f%%)\n", c[0], c[1],
+                 100.0 * (double)c[1] / (double)(c[0] + c[1] + 1));
   return nw;
 }
 

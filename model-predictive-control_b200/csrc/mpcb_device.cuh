@@ -18,7 +18,7 @@ namespace mpcb {
 
 // Everything the kernels need from MpcProblemDesc, passed by value (constant bank).
 struct KDesc {
-  int model_id, N, S, n_sub, nx, n, m, n_obs, flags, road_mode, n_roads, bounded;
+  int model_id, N, S, n_sub, nx, n, m, n_obs, flags, road_mode, n_roads, bounded, debug;
   double h, Ts, v_ref, c[6];
   double kin_acc, kin_mu;
   double lane_a, lane_y_t, lane_b, lane_y_br, lane_y_bl;
@@ -45,6 +45,8 @@ MPCB_DEV void load_vehicle(VehP* v, const double* __restrict__ p, const KDesc& d
 
 // Problem description and vehicle constants of the running kernel, at file scope in shared memory so the
 // non-inlined evaluation function (mpcb_fwd.cuh) reads them with LDS instead of through generic pointers.
+// MPCB_DEBUG_TIMERS diagnostics: model calls that took the fast / general path (lane granularity)
+__device__ unsigned long long g_dbg_calls[2];
 static __shared__ VehP s_veh;
 static __shared__ KDesc s_desc;
 // Called by every thread of a kernel before it evaluates anything (ends with a block barrier).

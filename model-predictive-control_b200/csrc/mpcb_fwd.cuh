@@ -127,7 +127,9 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     const double a_f = fma(q[3], v.lf, q[2]), a_r = fma(q[3], v.lr, -q[2]);
     const double am = fmax(fabs(a_f), fabs(a_r));
     const bool ok = vx > 0x1p-960 && vx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX;
-    if (ok && su.z2_mode == 2 && am <= 0.5 * vx) call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
+    const bool fast = ok && su.z2_mode == 2 && am <= 0.5 * vx;
+    if (s_desc.debug) atomicAdd(&g_dbg_calls[fast ? 0 : 1], 1ull);
+    if (fast) call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
     else call_slow<GRAD>(q, su, v, a_f, a_r, kp, kq, L);  // slip beyond atan(0.5) = 26.6 deg, reversing, ...
   }
   // tangent of one direction J at the same stage point: tq = (phi', vx', vy', w')
@@ -310,7 +312,6 @@ template <int MODEL, bool GRAD>
 __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, Vec U, Vec scr, Vec grad, bool store,
                                        Vec states = Vec{nullptr, 0}, IVec idx_out = IVec{nullptr, 0}) {
   const KDesc& d = s_desc;
-  const VehP& v = s_veh;
   using M = Fm<MODEL>;
   constexpr int NX = M::NX, ND = M::ND, K = fm_stage_doubles<MODEL>();
   double y[NX];

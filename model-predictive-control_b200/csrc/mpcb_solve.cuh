@@ -13,6 +13,9 @@
 //     Appendix A 3d at once for G = 8), then its own psi(x̂+); the first accepted candidate in
 //     sequential order wins — the same decisions as sequential back-tracking because every trial
 //     restarts from the iterate's (L, gamma);
+//   * the finite-difference Hessian-vector gradient of the NEXT iteration (Appendix A 3c) is evaluated by the
+//     upper half of the tile in the same round in which the lower half evaluates psi(x̂+) of the first
+//     G/2 candidates: a typical iteration is two rounds (candidates, then psi(x̂+) || FD) instead of three;
 //   * descent lemma at k = 0: lane j evaluates psi(x̂(gamma / 2^j));
 //   * Lipschitz estimate: lane 1 evaluates grad psi(x + h) while lane 0 evaluates grad psi(x).
 // Every lane of a tile runs the same state machine on the same data (redundantly — free in SIMT), so
@@ -121,6 +124,9 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   bool exhausted = false;
   int64_t b = -1;
   int cl = 0, cb = 0;  // the iterate (x, g, x̂, p) lives in lane cl's bank cb
+  constexpr int H = G >= 2 ? G / 2 : G;  // candidates whose psi(x̂+) is evaluated first; lanes >= H speculate the FD gradient
+  bool fd_ready = false;                 // the next iteration's FD gradient is already in lane fd_lane's P row of bank cb
+  int fd_lane = 0, ge_row = 0, ge_lane = 0;
   int k = 0, no_prog = 0, lb_idx = 0, lb_full = 0, hb = 0, lsb = 0;
   double psi = 0, psi_hat = 0, gTp = 0, pTp = 0, L = 0, gam = 0, phi = 0, tau0 = 0, sigma = 0, hfd = 0, hh = 0;
   double eps_tol = 0, peps = 0, ppsi = 0, norm_e2 = 0;
@@ -131,7 +137,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   int want = 0, n_val = 0, n_grad = 0;
   Vec evp{nullptr, 0}, evg{nullptr, 0};
   double val = 0;
-  bool c_valid = false, c_pend = false, c_rq = false, c_fb = false, c_acc = false;
+  bool c_valid = false, c_pend = false, c_rq = false, c_fb = false, c_acc = false, c_started = false, fd_done = false;
   double psi_n = 0, psi_hat_n = 0, gTp_n = 0, pTp_n = 0, L_n = 0, gam_n = 0, phi_n = 0;
 
   // x̂ = Π_C(x − γ g), p = x̂ − x (stored into XH, P); returns gᵀp and pᵀp
@@ -139,7 +145,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     double s1 = 0.0, s2 = 0.0;
     for (int i = 0; i < n; ++i) {
       double xi = X(i), gi = Gv(i);
-      double t = xi - gamma * gi;
+      double t = fma(-gamma, gi, xi);
       t = t < lbv[i] ? lbv[i] : (t > ubv[i] ? ubv[i] : t);
       double pi = t - xi;
       XH.set(i, t);
@@ -266,7 +272,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           if (l == pl) XE.set(i, xi + h);
           hh += h * h;
         }
-        k = 0; no_prog = 0; lb_idx = 0; lb_full = 0;
+        k = 0; no_prog = 0; lb_idx = 0; lb_full = 0; fd_ready = false;
         if (G >= 2) {
           if (l == 0) { evp = X; evg = WL(M.G(cb), cl); want = 2; }
           else if (l == 1) { evp = XE; evg = WL(M.G(cb ^ 1), 1); want = 2; }
@@ -341,10 +347,10 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         double xx = 0.0;
         for (int i = 0; i < n; ++i) {
           double xi = X(i);
-          double gd = xi - gam * Gc(i);
+          double gd = fma(-gam, Gc(i), xi);
           bool active = gd < lbv[i] || ubv[i] < gd;
           if (!active) { ++nJ; if (i < 64) mask0 |= 1ull << i; else mask1 |= 1ull << (i - 64); }
-          xx += xi * xi;
+          xx = fma(xi, xi, xx);
         }
         const bool use_fd = sp.hess_vec_fd && nJ > 0 && nJ < n;
         for (int j = 0; j < ne; ++j) {
@@ -353,19 +359,27 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         }
         if (use_fd) {
           hfd = 6.0554544523933395e-06 /* cbrt(DBL_EPSILON) */ * (1.0 + sqrt(xx));
+          if (fd_ready) {  // evaluated speculatively during the previous line search (same point, bit for bit)
+            fd_ready = false;
+            ge_row = M.P(cb); ge_lane = fd_lane;
+            state = ST_FD_DONE;
+            continue;
+          }
           if (l == 0) {  // q is p on the active set and 0 on the inactive set at this point
             Vec XE = WL(M.X(cb ^ 1), 0);
-            for (int i = 0; i < n; ++i) XE.set(i, X(i) + hfd * (mbit(i) ? 0.0 : P(i)));
+            for (int i = 0; i < n; ++i) XE.set(i, fma(hfd, mbit(i) ? 0.0 : P(i), X(i)));
             evp = XE; evg = WL(M.G(cb ^ 1), 0); want = 2;
           }
+          ge_row = M.G(cb ^ 1); ge_lane = 0;
           state = ST_FD_DONE;
           break;
         }
+        fd_ready = false;
         if (nJ > 0) lbfgs_apply();
         tsync();  // every lane reads the whole q next
         state = ST_LS_START;
       } else if (state == ST_FD_DONE) {
-        Vec Gc = WL(M.G(cb), cl), GE = WL(M.G(cb ^ 1), 0);
+        Vec Gc = WL(M.G(cb), cl), GE = WL(ge_row, ge_lane);
         for (int j = 0; j < ne; ++j) {
           int e = l + G * j;
           if (e < n && mbit(e)) { double gi = Gc(e); tv(T.Q, e) = -gi - (GE(e) - gi) / hfd; }
@@ -391,7 +405,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         const int nb = cb ^ 1;
         c_fb = tau0 == 0.0 ? true : c == 8;
         c_valid = tau0 == 0.0 ? c == 0 : c <= 8;
-        c_pend = c_valid; c_rq = c_valid; c_acc = false;
+        c_pend = c_valid; c_rq = false; c_acc = false; c_started = false; fd_done = false;
         if (c_valid) {
           Vec XN = WL(M.X(nb), l);
           if (c_fb) {
@@ -408,11 +422,42 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         break;
       } else if (state == ST_LS_G_DONE) {
         const int nb = cb ^ 1;
-        if (c_valid) {
-          psi_n = val;
-          L_n = L; gam_n = gam;
-          prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
-          evp = WL(M.XH(nb), l); want = 1;
+        if (c_valid) { psi_n = val; L_n = L; gam_n = gam; }
+        if (l < H) {
+          if (c_valid) {
+            prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
+            evp = WL(M.XH(nb), l); want = 1; c_rq = true; c_started = true;
+          }
+        } else if (sp.hess_vec_fd) {
+          // upper half: psi(x̂+) of candidates >= H is deferred (needed only when candidates 0..H-1 all fail);
+          // meanwhile speculate the next iteration's FD gradient for candidate j = l - H, exactly as
+          // ST_ITER_TOP would form it if j is accepted with its step size unchanged
+          const int j = l - H;
+          const int cj = lsb * G + j;
+          const bool j_valid = tau0 == 0.0 ? cj == 0 : cj <= 8;
+          if (j_valid) {
+            Vec Xj = WL(M.X(nb), j), Gj = WL(M.G(nb), j);
+            int nJ = 0;
+            double xx = 0.0;
+            for (int i = 0; i < n; ++i) {
+              double xi = Xj(i);
+              double gd = fma(-gam, Gj(i), xi);
+              if (!(gd < lbv[i] || ubv[i] < gd)) ++nJ;
+              xx = fma(xi, xi, xx);
+            }
+            if (nJ > 0 && nJ < n) {
+              const double hf = 6.0554544523933395e-06 * (1.0 + sqrt(xx));
+              Vec XE = WL(M.XH(nb), l);
+              for (int i = 0; i < n; ++i) {
+                double xi = Xj(i);
+                double gd = fma(-gam, Gj(i), xi);
+                bool active = gd < lbv[i] || ubv[i] < gd;
+                double t = gd < lbv[i] ? lbv[i] : (gd > ubv[i] ? ubv[i] : gd);
+                XE.set(i, fma(hf, active ? t - xi : 0.0, xi));
+              }
+              evp = XE; evg = WL(M.P(nb), l); want = 2; fd_done = true;
+            }
+          }
         }
         state = ST_LS_V_DONE;
         break;
@@ -437,8 +482,14 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         const unsigned am = (__ballot_sync(tmask, c_valid && !c_pend && c_acc) & tmask) >> tbase;
         const int first_acc = am ? __ffs(am) - 1 : G;
         const unsigned below = (1u << first_acc) - 1u;  // first_acc <= G <= 8
-        if (pm & below) {  // an earlier candidate is still shrinking its step: it is decided first
-          if (c_valid && c_pend && l < first_acc) { evp = WL(M.XH(nb), l); want = 1; c_rq = true; }
+        if (pm & below) {  // earlier candidates are undecided (shrinking their step, or deferred): they go first
+          if (c_valid && c_pend && l < first_acc) {
+            if (!c_started) {  // deferred candidate: its speculative FD result (if any) is dropped
+              prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
+              c_started = true; fd_done = false;
+            }
+            evp = WL(M.XH(nb), l); want = 1; c_rq = true;
+          }
           break;
         }
         if (first_acc == G) { ++lsb; state = ST_LS_REQ; continue; }  // all rejected: next batch of candidates
@@ -467,6 +518,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
             if (++lb_idx == mem) { lb_idx = 0; lb_full = 1; }
           }
           if (no_prog > 0 || k % sp.max_no_progress == 0) no_prog = same ? no_prog + 1 : 0;
+        }
+        {
+          const unsigned fdm = (__ballot_sync(tmask, fd_done) & tmask) >> tbase;
+          const double gam_w = tbcast(gam_n, jw);
+          fd_ready = G >= 2 && jw < H && ((fdm >> ((jw + H) & 31)) & 1u) && gam_w == gam;
+          fd_lane = jw + H;
         }
         psi = tbcast(psi_n, jw); psi_hat = tbcast(psi_hat_n, jw);
         gTp = tbcast(gTp_n, jw); pTp = tbcast(pTp_n, jw);

@@ -81,6 +81,15 @@ int main() {
       first = false;
     }
   }
+  printf("],\n\"dfma_warps_per_sm\": [");
+  first = true;
+  for (int w : {1, 2, 3, 4, 6, 8}) {   // warps on ONE SM (round-robin over its 4 sub-partitions), all lanes active
+    k_dfma<<<1, 32 * w>>>(out, iters, 32, cyc);
+    k_dfma<<<1, 32 * w>>>(out, iters, 32, cyc);
+    long long c; cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
+    printf("%s{\"warps_per_sm\": %d, \"cycles_per_warp_dfma\": %.3f}", first ? "" : ", ", w, (double)c / (iters * 8.0));
+    first = false;
+  }
   printf("],\n");
   cudaMemset(err, 0, 32);
   k_rcp<<<148, 256>>>(err, 1 << 24);
