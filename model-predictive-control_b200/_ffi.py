@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmpcb200.so")
+# MPCB_LIB: another build of the same ABI (A/B timing of kernel variants); default is the in-tree library
+LIB_PATH = os.environ.get("MPCB_LIB") or os.path.join(_HERE, "libmpcb200.so")
 
 # model / road / flag constants (include/mpcb200.h)
 MODEL_PACEJKA6, MODEL_KINEMATIC4 = 0, 1

@@ -492,7 +492,7 @@ int64_t mpcb_debug_timers(MpcHandle* h, long long* out, int64_t max_warps) {
   if (cudaDeviceSynchronize() != cudaSuccess) return 0;
   if (cudaMemcpy(out, h->dbg, (size_t)nw * 4 * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return 0;
   unsigned long long c[2] = {0, 0};
-  if (cudaMemcpyFromSymbol(c, g_dbg_calls, sizeof(c)) == cudaSuccess)
+  if (h->debug_timers >= 2 && cudaMemcpyFromSymbol(c, g_dbg_calls, sizeof(c)) == cudaSuccess)
     std::fprintf(stderr, "[mpcb debug] model calls: fast path %llu, general path %llu (%.2f%%)\n", c[0], c[1],
                  100.0 * (double)c[1] / (double)(c[0] + c[1] + 1));
   return nw;

@@ -128,7 +128,7 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     const double am = fmax(fabs(a_f), fabs(a_r));
     const bool ok = vx > 0x1p-960 && vx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX;
     const bool fast = ok && su.z2_mode == 2 && am <= 0.5 * vx;
-    if (s_desc.debug) atomicAdd(&g_dbg_calls[fast ? 0 : 1], 1ull);
+    if (s_desc.debug >= 2) atomicAdd(&g_dbg_calls[fast ? 0 : 1], 1ull);  // MPCB_DEBUG_TIMERS=2
     if (fast) call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
     else call_slow<GRAD>(q, su, v, a_f, a_r, kp, kq, L);  // slip beyond atan(0.5) = 26.6 deg, reversing, ...
   }

@@ -53,7 +53,7 @@ struct SolveArgs {
 
 enum SolveState {
   ST_IDLE = 0, ST_START_PANOC, ST_INIT_G1, ST_LIP_DONE, ST_XHAT_REQ, ST_XHAT_DONE, ST_ITER_TOP, ST_FD_DONE,
-  ST_LS_START, ST_LS_REQ, ST_LS_G_DONE, ST_LS_V_DONE, ST_PANOC_EXIT, ST_ALM_V, ST_ALM_UPDATE
+  ST_LS_START, ST_LS_STEP, ST_PANOC_EXIT, ST_ALM_V, ST_ALM_UPDATE
 };
 
 // Per-lane workspace rows (units: doubles per lane).
@@ -127,7 +127,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   constexpr int H = G >= 2 ? G / 2 : G;  // candidates whose psi(x̂+) is evaluated first; lanes >= H speculate the FD gradient
   bool fd_ready = false;                 // the next iteration's FD gradient is already in lane fd_lane's P row of bank cb
   int fd_lane = 0, ge_row = 0, ge_lane = 0;
-  int k = 0, no_prog = 0, lb_idx = 0, lb_full = 0, hb = 0, lsb = 0;
+  int k = 0, no_prog = 0, lb_idx = 0, lb_full = 0, hb = 0, lsw = 0;
+  unsigned specmask = 0;                 // candidates (by lane) whose FD speculation has been handed out
   double psi = 0, psi_hat = 0, gTp = 0, pTp = 0, L = 0, gam = 0, phi = 0, tau0 = 0, sigma = 0, hfd = 0, hh = 0;
   double eps_tol = 0, peps = 0, ppsi = 0, norm_e2 = 0;
   int alm_i = 0, inner_total = 0, pstatus = 0;
@@ -138,6 +139,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   Vec evp{nullptr, 0}, evg{nullptr, 0};
   double val = 0;
   bool c_valid = false, c_pend = false, c_rq = false, c_fb = false, c_acc = false, c_started = false, fd_done = false;
+  bool c_needg = false;
+  int c_idx = 0, spec_for = -1;
   double psi_n = 0, psi_hat_n = 0, gTp_n = 0, pTp_n = 0, L_n = 0, gam_n = 0, phi_n = 0;
 
   // x̂ = Π_C(x − γ g), p = x̂ − x (stored into XH, P); returns gᵀp and pᵀp
@@ -205,6 +208,45 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         int e = l + G * j;
         if (e < n && mbit(e)) tv(T.Q, e) += coef * tv(T.LS + i * T.np, e);
       }
+    }
+  };
+
+  // Line-search candidates (Appendix A 3d): c = 0..7 -> tau = 2^-c, c = 8 -> the prox step x̂ (forced
+  // accept).  Lane order is trial order: the last lane of the tile holds c = 8 from the start (long runs of
+  // iterations in which every tau fails are what the slowest instances of a batch are made of), the
+  // lanes below it hold a window of G-1 consecutive tau candidates, right-aligned, that slides when all
+  // of its candidates are rejected.  G = 1: one candidate at a time, c = lsw.  tau0 = 0 (k = 0 or a
+  // non-finite q): only the prox step.  Newly assigned candidates request psi and grad psi.
+  auto ls_assign = [&](bool first) {
+    const int nb = cb ^ 1;
+    bool mine = false, valid = false;
+    if (G == 1) {
+      c_idx = tau0 == 0.0 ? 8 : lsw;
+      mine = true; valid = true;
+    } else if (l == G - 1) {
+      if (first) { c_idx = 8; mine = true; valid = true; }
+    } else {
+      const int c_first = lsw * (G - 1);
+      const int cnt = 8 - c_first < G - 1 ? 8 - c_first : G - 1;
+      const int j = l - (G - 1 - cnt);
+      c_idx = c_first + j;
+      mine = true; valid = tau0 != 0.0 && j >= 0;
+    }
+    if (!mine) return;
+    c_fb = c_idx == 8;
+    c_valid = valid; c_pend = valid; c_needg = valid;
+    c_rq = false; c_acc = false; c_started = false;
+    if (valid) {
+      Vec XN = WL(M.X(nb), l);
+      if (c_fb) {
+        Vec XH = WL(M.XH(cb), cl);
+        for (int i = 0; i < n; ++i) XN.set(i, XH(i));
+      } else {
+        const double tau = ldexp(1.0, -c_idx);
+        Vec X = WL(M.X(cb), cl), P = WL(M.P(cb), cl);
+        for (int i = 0; i < n; ++i) XN.set(i, X(i) + (1.0 - tau) * P(i) + tau * tv(T.Q, i));
+      }
+      evp = XN; evg = WL(M.G(nb), l); want = 2;
     }
   };
 
@@ -396,103 +438,123 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           if (!fin) { tau0 = 0.0; lb_idx = 0; lb_full = 0; }
         }
         sigma = (1.0 - gam * L) * pTp / (2.0 * gam);
-        lsb = 0;
-        state = ST_LS_REQ;
-      } else if (state == ST_LS_REQ) {
-        // line-search candidates (Appendix A 3d): c = 0..7 -> tau = 2^-c, c = 8 -> the prox step x̂
-        // (forced accept); tau0 = 0 (k = 0 or non-finite q) -> only the prox step.
-        const int c = lsb * G + l;
-        const int nb = cb ^ 1;
-        c_fb = tau0 == 0.0 ? true : c == 8;
-        c_valid = tau0 == 0.0 ? c == 0 : c <= 8;
-        c_pend = c_valid; c_rq = false; c_acc = false; c_started = false; fd_done = false;
-        if (c_valid) {
-          Vec XN = WL(M.X(nb), l);
-          if (c_fb) {
-            Vec XH = WL(M.XH(cb), cl);
-            for (int i = 0; i < n; ++i) XN.set(i, XH(i));
-          } else {
-            const double tau = ldexp(1.0, -c);
-            Vec X = WL(M.X(cb), cl), P = WL(M.P(cb), cl);
-            for (int i = 0; i < n; ++i) XN.set(i, X(i) + (1.0 - tau) * P(i) + tau * tv(T.Q, i));
-          }
-          evp = XN; evg = WL(M.G(nb), l); want = 2;
-        }
-        state = ST_LS_G_DONE;
+        lsw = 0; specmask = 0;
+        fd_done = false; spec_for = -1;
+        ls_assign(true);
+        state = ST_LS_STEP;
         break;
-      } else if (state == ST_LS_G_DONE) {
+      } else if (state == ST_LS_STEP) {
+        // One decision step of the line search (Appendix A 3d), run after every evaluation round.
         const int nb = cb ^ 1;
-        if (c_valid) { psi_n = val; L_n = L; gam_n = gam; }
-        if (l < H) {
-          if (c_valid) {
+        const double thr = (1.0 + fabs(phi)) * sp.ls_tol;
+        if (c_valid && c_pend) {
+          if (c_needg) {  // psi, grad psi of this lane's candidate arrived: x̂+, p+ and the tentative phi+
+            c_needg = false;
+            psi_n = val; L_n = L; gam_n = gam;
             prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
-            evp = WL(M.XH(nb), l); want = 1; c_rq = true; c_started = true;
-          }
-        } else if (sp.hess_vec_fd) {
-          // upper half: psi(x̂+) of candidates >= H is deferred (needed only when candidates 0..H-1 all fail);
-          // meanwhile speculate the next iteration's FD gradient for candidate j = l - H, exactly as
-          // ST_ITER_TOP would form it if j is accepted with its step size unchanged
-          const int j = l - H;
-          const int cj = lsb * G + j;
-          const bool j_valid = tau0 == 0.0 ? cj == 0 : cj <= 8;
-          if (j_valid) {
-            Vec Xj = WL(M.X(nb), j), Gj = WL(M.G(nb), j);
-            int nJ = 0;
-            double xx = 0.0;
-            for (int i = 0; i < n; ++i) {
-              double xi = Xj(i);
-              double gd = fma(-gam, Gj(i), xi);
-              if (!(gd < lbv[i] || ubv[i] < gd)) ++nJ;
-              xx = fma(xi, xi, xx);
+            c_started = true; fd_done = false;
+            if (!c_fb) {
+              // phi_gamma(x+) = psi + min_z {g'(z - x+) + |z - x+|^2 / (2 gamma)} can only grow when the
+              // descent lemma shrinks gamma, so a candidate that fails the line-search test with the
+              // iterate's gamma (beyond a 1e-10 rounding guard) fails it for every smaller gamma: it is
+              // rejected here, without evaluating psi(x̂+).  NaN fails (same as the sequential test).
+              const double lc = psi_n + pTp_n / (2.0 * gam_n) + gTp_n - (phi - sigma);
+              if (!(lc <= thr + 1e-10 * (1.0 + fabs(phi)))) { c_pend = false; c_acc = false; }
             }
-            if (nJ > 0 && nJ < n) {
-              const double hf = 6.0554544523933395e-06 * (1.0 + sqrt(xx));
-              Vec XE = WL(M.XH(nb), l);
-              for (int i = 0; i < n; ++i) {
-                double xi = Xj(i);
-                double gd = fma(-gam, Gj(i), xi);
-                bool active = gd < lbv[i] || ubv[i] < gd;
-                double t = gd < lbv[i] ? lbv[i] : (gd > ubv[i] ? ubv[i] : gd);
-                XE.set(i, fma(hf, active ? t - xi : 0.0, xi));
-              }
-              evp = XE; evg = WL(M.P(nb), l); want = 2; fd_done = true;
+          } else if (c_rq) {  // psi(x̂+) arrived: descent lemma at x+, then the line-search test
+            psi_hat_n = val;
+            const double margin = (1.0 + fabs(psi_n)) * sp.quad_tol;
+            if (psi_hat_n - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max) {
+              L_n *= 2.0; gam_n *= 0.5;  // shrink this candidate's step and re-evaluate
+              prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
+              fd_done = false;
+            } else {
+              c_pend = false;
+              phi_n = psi_n + pTp_n / (2.0 * gam_n) + gTp_n;
+              // NaN-safe: a non-finite phi+ is a failed trial (keeps back-tracking to the prox step)
+              c_acc = c_fb || (phi_n - (phi - sigma) <= thr);
             }
-          }
-        }
-        state = ST_LS_V_DONE;
-        break;
-      } else if (state == ST_LS_V_DONE) {
-        const int nb = cb ^ 1;
-        if (c_valid && c_pend && c_rq) {
-          psi_hat_n = val;
-          double margin = (1.0 + fabs(psi_n)) * sp.quad_tol;
-          if (psi_hat_n - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max) {
-            L_n *= 2.0; gam_n *= 0.5;  // descent lemma at x⁺: shrink this candidate's step and re-evaluate
-            prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
-          } else {
-            c_pend = false;
-            phi_n = psi_n + pTp_n / (2.0 * gam_n) + gTp_n;
-            double ls_cond = phi_n - (phi - sigma);
-            // NaN-safe: a non-finite phi+ is a failed trial (keeps back-tracking to the prox step)
-            c_acc = c_fb || (ls_cond <= (1.0 + fabs(phi)) * sp.ls_tol);
           }
         }
         c_rq = false;
-        const unsigned pm = (__ballot_sync(tmask, c_valid && c_pend) & tmask) >> tbase;
+        unsigned pm = (__ballot_sync(tmask, c_valid && c_pend) & tmask) >> tbase;
         const unsigned am = (__ballot_sync(tmask, c_valid && !c_pend && c_acc) & tmask) >> tbase;
         const int first_acc = am ? __ffs(am) - 1 : G;
         const unsigned below = (1u << first_acc) - 1u;  // first_acc <= G <= 8
-        if (pm & below) {  // earlier candidates are undecided (shrinking their step, or deferred): they go first
-          if (c_valid && c_pend && l < first_acc) {
-            if (!c_started) {  // deferred candidate: its speculative FD result (if any) is dropped
+        // the window of tau candidates slides once all of its lanes are rejected (the prox step on the last
+        // lane cannot be accepted before every tau has been tried)
+        const unsigned wmask = (1u << (G - 1)) - 1u;
+        const bool slide = G >= 2 && !((pm | am) & wmask) && tau0 != 0.0 && (lsw + 1) * (G - 1) <= 7;
+        if (pm & below || first_acc == G || slide) {
+          // earlier candidates are undecided (or, G = 1, the only candidate was rejected): another round
+          if (G == 1) {
+            if (!c_pend) { ++lsw; ls_assign(false); }
+          } else {
+            if (slide) {
+              ++lsw;
+              ls_assign(false);
+              // speculations made for the window's previous candidates are void
+              if (spec_for >= 0 && spec_for < G - 1) { fd_done = false; spec_for = -1; }
+              specmask &= ~wmask;
+              pm = (__ballot_sync(tmask, c_valid && c_pend) & tmask) >> tbase;
+            }
+          }
+          const unsigned needg = (__ballot_sync(tmask, c_valid && c_pend && c_needg) & tmask) >> tbase;
+          // primary candidates: the first H undecided ones evaluate psi(x̂+) in this round
+          unsigned primary = 0;
+          {
+            unsigned cand = pm & below & ~needg;
+            for (int r = 0; r < H && cand; ++r) { unsigned low = cand & (0u - cand); primary |= low; cand ^= low; }
+          }
+          if ((primary >> l) & 1u) {
+            if (!c_started) {  // deferred candidate (its rows were lent to an FD speculation)
               prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
               c_started = true; fd_done = false;
             }
             evp = WL(M.XH(nb), l); want = 1; c_rq = true;
           }
+          if (G >= 2 && sp.hess_vec_fd) {
+            // Speculate the next iteration's FD gradient for primary candidates on lanes with nothing to
+            // evaluate in this round, exactly as ST_ITER_TOP would form it if the candidate is accepted
+            // with its step size unchanged: the r-th free lane serves the r-th primary candidate.
+            const unsigned holds = (__ballot_sync(tmask, fd_done) & tmask) >> tbase;
+            const unsigned tbits = (G >= 32) ? 0xffffffffu : ((1u << G) - 1u);
+            unsigned fr = tbits & ~(primary | needg | holds | am);  // decided-and-waiting lanes keep their x̂+, p+
+            unsigned ts = primary & ~specmask;
+            int target = -1;
+            while (fr && ts) {
+              const int fl = __ffs(fr) - 1, tl = __ffs(ts) - 1;
+              if (fl == l) target = tl;
+              fr &= fr - 1; ts &= ts - 1;
+              specmask |= 1u << tl;
+            }
+            if (target >= 0) {
+              Vec Xj = WL(M.X(nb), target), Gj = WL(M.G(nb), target);
+              int nJ = 0;
+              double xx = 0.0;
+              for (int i = 0; i < n; ++i) {
+                double xi = Xj(i);
+                double gd = fma(-gam, Gj(i), xi);
+                if (!(gd < lbv[i] || ubv[i] < gd)) ++nJ;
+                xx = fma(xi, xi, xx);
+              }
+              if (nJ > 0 && nJ < n) {
+                const double hf = 6.0554544523933395e-06 * (1.0 + sqrt(xx));
+                Vec XE = WL(M.XH(nb), l);
+                for (int i = 0; i < n; ++i) {
+                  double xi = Xj(i);
+                  double gd = fma(-gam, Gj(i), xi);
+                  bool active = gd < lbv[i] || ubv[i] < gd;
+                  double t = gd < lbv[i] ? lbv[i] : (gd > ubv[i] ? ubv[i] : gd);
+                  XE.set(i, fma(hf, active ? t - xi : 0.0, xi));
+                }
+                evp = XE; evg = WL(M.P(nb), l); want = 2; fd_done = true; spec_for = target;
+                c_started = false;  // this lane's own x̂+, p+ rows now hold the speculation
+              }
+            }
+          }
           break;
         }
-        if (first_acc == G) { ++lsb; state = ST_LS_REQ; continue; }  // all rejected: next batch of candidates
         // accept candidate jw: L-BFGS update with s = x⁺ − x, y = ∇ψ⁺ − ∇ψ (Appendix A 3e)
         const int jw = first_acc;
         {
@@ -520,10 +582,10 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           if (no_prog > 0 || k % sp.max_no_progress == 0) no_prog = same ? no_prog + 1 : 0;
         }
         {
-          const unsigned fdm = (__ballot_sync(tmask, fd_done) & tmask) >> tbase;
+          const unsigned fdm = (__ballot_sync(tmask, fd_done && spec_for == jw) & tmask) >> tbase;
           const double gam_w = tbcast(gam_n, jw);
-          fd_ready = G >= 2 && jw < H && ((fdm >> ((jw + H) & 31)) & 1u) && gam_w == gam;
-          fd_lane = jw + H;
+          fd_ready = G >= 2 && fdm != 0 && gam_w == gam;
+          fd_lane = fdm ? __ffs(fdm) - 1 : 0;
         }
         psi = tbcast(psi_n, jw); psi_hat = tbcast(psi_hat_n, jw);
         gTp = tbcast(gTp_n, jw); pTp = tbcast(pTp_n, jw);

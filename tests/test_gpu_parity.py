@@ -220,6 +220,27 @@ def test_solve_iteration_counts_track_oracle(mp, orc):
     assert abs(np.median(gi) - np.median(r["inner"])) <= 3
 
 
+@pytest.mark.parametrize("G", [8, 4, 2, 1])
+def test_every_tile_width_tracks_oracle(mp, orc, G, monkeypatch):
+    """The tile width (lanes per instance; picked from the batch size, forced here with MPCB_TILE) only changes
+    how much of the line search is speculated, never its decisions: every width must take the oracle's
+    iteration counts (a width that skips a back-tracking trial still converges, just along another path)."""
+    from mpcb200 import workloads as wl
+    monkeypatch.setenv("MPCB_TILE", str(G))
+    N, B, S = 20, 256, 100
+    w = wl.tracking_batch(B, N, S, seed=5)
+    prob = mp.BatchedMpc(N=N, S=S, road_mode=mp.ROAD_TABLE, n_roads=2)
+    U, _, stats = prob.solve(w["x0"], w["road"], w["U0"].copy(), road_idx=w["road_idx"])
+    r = orc.solve(_desc(orc, 0, N, S, 1, 2), orc.default_solver_params(N), w["x0"], w["road"], w["U0"],
+                  road_idx=w["road_idx"])
+    gi = stats.inner_iterations.cpu().numpy()
+    same = (gi == r["inner"]).mean()
+    print(f"G={G}: identical inner-iteration counts {same:.3f}; mean gpu {gi.mean():.2f} oracle {r['inner'].mean():.2f}")
+    assert (stats.status.cpu().numpy() == 1).all()
+    assert same > 0.3   # N = 20 solves are long enough for 1-ulp libm differences to change some paths
+    assert abs(gi.mean() - r["inner"].mean()) < 0.03 * r["inner"].mean()
+
+
 def test_solve_host_equals_solve_device(mp, orc):
     from mpcb200 import workloads as wl
     N, B = 12, 100
