@@ -78,6 +78,11 @@ KDesc make_kdesc(const MpcProblemDesc& d) {
   k.obs_Af = d.obs_Af; k.obs_b = d.obs_b; k.obs_sx = d.obs_sigma_x; k.obs_sy = d.obs_sigma_y; k.obs_adiv = d.obs_alpha_div;
   k.bounded = 0;
   k.debug = 0;
+  // psi = sum of c_i * (error)^2 + lane potentials + obstacle Gaussians + Sigma/2 dist^2 (mpcb_cost.cuh)
+  k.psi_nonneg = 1;
+  for (int i = 0; i < 6; ++i) if (!(d.c[i] >= 0.0)) k.psi_nonneg = 0;
+  if ((d.flags & MPCB_FLAG_LANE) && !(d.lane_a >= 0.0 && d.lane_b >= 0.0)) k.psi_nonneg = 0;
+  if ((d.flags & MPCB_FLAG_OBST) && !(d.obs_Af >= 0.0)) k.psi_nonneg = 0;
   if (d.flags & MPCB_FLAG_BOUNDED_D)
     for (int i = 0; i < k.nx; ++i)
       if (!std::isinf(d.D_lower[i]) || !std::isinf(d.D_upper[i])) k.bounded = 1;
@@ -92,12 +97,12 @@ int prepare_road(MpcHandle* h, int64_t B, const double* road, const int32_t* roa
   *smem_bytes = 0;
   switch (h->kd.road_mode) {
     case MPCB_ROAD_SHARED:
-      ra->in_smem = 1; ra->R = 1; *smem_bytes = (size_t)S * 16;
+      ra->in_smem = 1; ra->R = 1; *smem_bytes = (size_t)road_smem_doubles(S) * sizeof(double);
       return 0;
     case MPCB_ROAD_TABLE:
       if (!road_idx) return fail(h, MPCB_E_ARG, "road_idx is required for MPCB_ROAD_TABLE");
       ra->in_smem = 1; ra->R = h->kd.n_roads; ra->road_idx = road_idx;
-      *smem_bytes = (size_t)ra->R * S * 16;
+      *smem_bytes = (size_t)ra->R * road_smem_doubles(S) * sizeof(double);
       if (*smem_bytes > 160 * 1024) return fail(h, MPCB_E_UNSUPPORTED, "road table exceeds 160 KB of shared memory");
       return 0;
     case MPCB_ROAD_PER_INSTANCE: {

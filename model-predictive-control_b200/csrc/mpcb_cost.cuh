@@ -17,6 +17,9 @@ struct RoadView {
   int64_t stride;
   unsigned sbase;
   int smem;
+  // shared-memory roads carry two derived tables behind the vertices (stage_roads, mpcb_eval.cuh):
+  // the heading of every segment, and an (xmin, xmax, ymin, ymax) box per chunk of MPCB_SCAN_CHUNK candidates
+  unsigned hbase, bbase;
   MPCB_DEV void xy(int i, double& x, double& y) const {
     if (smem) {
       asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(sbase + 16u * (unsigned)i));
@@ -30,12 +33,27 @@ struct RoadView {
 };
 
 #define MPCB_PI 3.141592653589793238462643383279502884
+#define MPCB_SCAN_CHUNK 8
+// doubles one staged road occupies in shared memory: S vertices (x, y), S headings, 4 per chunk box
+__host__ __device__ inline int road_box_offset(int S) { return (3 * S + 1) & ~1; }  // 16-byte aligned for any S
+__host__ __device__ inline int road_smem_doubles(int S) {
+  return road_box_offset(S) + 4 * ((S - 1 + MPCB_SCAN_CHUNK - 1) / MPCB_SCAN_CHUNK);
+}
 
-// np.mod(a + pi, 2 pi) - pi: floor-mod via fmod + sign fix (car_dynamics.py:168-172).
+// np.mod(a + pi, 2 pi) - pi: floor-mod via fmod + sign fix (car_dynamics.py:168-172).  fmod is exact, so
+// within one period either side it is the identity or one exact subtraction (Sterbenz); only angles
+// further out take the library loop.
 MPCB_DEV double wrap_to_pi(double a) {
   const double two_pi = 2.0 * MPCB_PI;
-  double m = fmod(a + MPCB_PI, two_pi);
-  if (m < 0.0) m += two_pi;
+  const double t = a + MPCB_PI;
+  double m;
+  if (t >= 0.0 && t < two_pi) m = t;
+  else if (t >= two_pi && t < 2.0 * two_pi) m = t - two_pi;
+  else if (t < 0.0 && t > -two_pi) m = t + two_pi;
+  else {
+    m = fmod(t, two_pi);
+    if (m < 0.0) m += two_pi;
+  }
   return m - MPCB_PI;
 }
 
@@ -130,8 +148,52 @@ __device__ __noinline__ int nearest_scan_strided(const double* rx, const double*
   if (nearest_scan_core(ScanLoadStrided{rx, ry, stride}, S, px, py, &best)) return best;
   return -1;
 }
-MPCB_DEV int nearest_scan(const RoadView& r, int S, double px, double py) {
-  int best = r.smem ? nearest_scan_shared(r.sbase, S, px, py) : nearest_scan_strided(r.rx, r.ry, r.stride, S, px, py);
+// Shared-memory roads: the same search, pruned.  The chunk holding `hint` (the previous stage's winner; the
+// vehicle moves a fraction of a segment per stage) is scanned first; every other chunk is scanned only if
+// the distance from (px, py) to its bounding box does not exceed the running minimum.  The box distance is
+// built from the same rounded operations as d2_of and is monotone in |dx|, |dy|, so it never exceeds the
+// d2 of a vertex inside the box; the 1e-15 slack keeps every vertex that could be a near-tie in the
+// scan, so the runner-up test (and the exact fallback behind it) sees what the full scan would see.
+// Returns -1 on a near-tie / NaN, like nearest_scan_shared.
+__device__ __noinline__ int nearest_scan_pruned(unsigned sbase, unsigned bbase, int S, double px, double py, int hint) {
+  const int n = S - 1;  // candidates 0 .. S-2
+  const int nc = (n + MPCB_SCAN_CHUNK - 1) / MPCB_SCAN_CHUNK;
+  const double inf = __longlong_as_double(0x7ff0000000000000LL);
+  double m = inf, second = inf;
+  int best = 0;
+  auto scan_chunk = [&](int c) {
+    const int i0 = c * MPCB_SCAN_CHUNK;
+#pragma unroll
+    for (int k = 0; k < MPCB_SCAN_CHUNK; ++k) {
+      const int i = i0 + k;
+      if (i < n) {
+        double x, y;
+        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(sbase + 16u * (unsigned)i));
+        const double dd = d2_of(x, y, px, py);
+        const bool lt = dd < m;
+        second = lt ? m : fmin(second, dd);
+        best = lt ? i : best;
+        m = lt ? dd : m;
+      }
+    }
+  };
+  const int hc = hint >= 0 && hint < n ? hint / MPCB_SCAN_CHUNK : 0;
+  scan_chunk(hc);
+#pragma unroll 1
+  for (int c = 0; c < nc; ++c) {
+    if (c == hc) continue;
+    double x0, x1, y0, y1;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x0), "=d"(x1) : "r"(bbase + 32u * (unsigned)c));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(y0), "=d"(y1) : "r"(bbase + 32u * (unsigned)c + 16u));
+    const double dx = fmax(fmax(x0 - px, px - x1), 0.0), dy = fmax(fmax(y0 - py, py - y1), 0.0);
+    const double lb = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+    if (!(lb > m * (1.0 + 1e-15))) scan_chunk(c);  // NaN: scan
+  }
+  return second > m * (1.0 + 4.5e-16) ? best : -1;
+}
+MPCB_DEV int nearest_scan(const RoadView& r, int S, double px, double py, int hint = -1) {
+  int best = r.smem ? nearest_scan_pruned(r.sbase, r.bbase, S, px, py, hint)
+                    : nearest_scan_strided(r.rx, r.ry, r.stride, S, px, py);
   if (best < 0) best = nearest_scan_exact(r, S, px, py);
   return best;
 }
@@ -155,6 +217,7 @@ struct RoadGeom {  // the three vertices the errors are built from, as differenc
   double wx, wy;    // nearest - previous
   double w2x, w2y;  // next - nearest
   double ax, ay;    // previous
+  double hd;        // atan2(w2y, w2x)
 };
 
 MPCB_DEV void road_geom(const RoadView& r, int idx, RoadGeom& g) {
@@ -166,6 +229,9 @@ MPCB_DEV void road_geom(const RoadView& r, int idx, RoadGeom& g) {
   r.xy(in, qx, qy);
   g.wx = g.nx - g.ax; g.wy = g.ny - g.ay;
   g.w2x = qx - g.nx; g.w2y = qy - g.ny;
+  // staged roads hold this very atan2 of these very operands per segment (stage_roads)
+  if (r.smem) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(g.hd) : "r"(r.hbase + 8u * (unsigned)idx));
+  else g.hd = atan2(g.w2y, g.w2x);
 }
 
 // car_dynamics.py:194-228: cte, heading error, positional error (raw cross products).
@@ -173,7 +239,7 @@ MPCB_DEV void road_errors(const RoadGeom& g, double px, double py, double phi, d
                           double* pe) {
   double vx = px - g.ax, vy = py - g.ay;
   *cte = vx * g.wy - vy * g.wx;
-  *he = wrap_to_pi(atan2(g.w2y, g.w2x) - phi);
+  *he = wrap_to_pi(g.hd - phi);
   double v2x = px - g.nx, v2y = py - g.ny;
   *pe = v2x * g.w2y - v2y * g.w2x;
 }
@@ -228,7 +294,7 @@ template <int MODEL, bool GRAD, bool SCAN>
 MPCB_DEV double stage_cost(const KDesc& d, const RoadView& r, const Extras& ex, int n, const double* y, double ud,
                            double udl, int* idx_io, double* gy, double* gu) {
   constexpr int NX = ModelTraits<MODEL>::NX;
-  int idx = SCAN ? nearest_scan(r, d.S, y[0], y[1]) : *idx_io;
+  int idx = SCAN ? nearest_scan(r, d.S, y[0], y[1], idx_io ? *idx_io : -1) : *idx_io;  // *idx_io in: search hint
   if (SCAN && idx_io) *idx_io = idx;
   RoadGeom g;
   road_geom(r, idx, g);

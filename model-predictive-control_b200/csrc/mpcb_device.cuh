@@ -19,6 +19,7 @@ namespace mpcb {
 // Everything the kernels need from MpcProblemDesc, passed by value (constant bank).
 struct KDesc {
   int model_id, N, S, n_sub, nx, n, m, n_obs, flags, road_mode, n_roads, bounded, debug;
+  int psi_nonneg;  // every cost term is a non-negative weight times a square / a Gaussian: psi >= 0 everywhere
   double h, Ts, v_ref, c[6];
   double kin_acc, kin_mu;
   double lane_a, lane_y_t, lane_b, lane_y_br, lane_y_bl;

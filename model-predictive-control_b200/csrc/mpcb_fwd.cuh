@@ -318,13 +318,13 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
 #pragma unroll
   for (int i = 0; i < NX; ++i) y[i] = x0[i];
   double cost = 0.0;
+  int idx = -1;  // nearest vertex of the previous stage: where the next search starts
 #pragma unroll 1
   for (int n = 0; n < d.N; ++n) {
     const double ud = U(2 * n), udl = U(2 * n + 1);
     const int o = n * K;
     stage_fm<MODEL, GRAD>(y, ud, udl, scr, o, store);
     double gy[NX], gu[2];
-    int idx;
     cost += stage_cost<MODEL, GRAD, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
     if (states.p) {
 #pragma unroll

@@ -60,7 +60,7 @@ __global__ void k_road_errors(KDesc d, int64_t B, const double* __restrict__ pos
   const double* base = road;
   if (d.road_mode == MPCB_ROAD_TABLE) base = road + (int64_t)(road_idx ? road_idx[b] : 0) * 2 * S;
   else if (d.road_mode == MPCB_ROAD_PER_INSTANCE) base = road + b * 2 * S;
-  RoadView r{base, base + S, 1, 0u, 0};
+  RoadView r{base, base + S, 1, 0u, 0, 0u, 0u};
   double px = pos[2 * b], py = pos[2 * b + 1], phi = heading[b];
   double cte, he, pe;
   int idx;
@@ -78,6 +78,7 @@ __global__ void k_road_errors(KDesc d, int64_t B, const double* __restrict__ pos
     g.ax = r.x(ip); g.ay = r.y(ip);
     g.wx = g.nx - g.ax; g.wy = g.ny - g.ay;
     g.w2x = r.x(in) - g.nx; g.w2y = r.y(in) - g.ny;
+    g.hd = atan2(g.w2y, g.w2x);
     road_errors(g, px, py, phi, &cte, &he, &pe);
     cte = cte / sqrt(g.wx * g.wx + g.wy * g.wy);
     pe = pe / sqrt(g.w2x * g.w2x + g.w2y * g.w2y);

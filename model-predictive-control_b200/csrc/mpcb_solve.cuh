@@ -87,7 +87,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   extern __shared__ double smem[];
   const int n = d.n, m = d.m, mem = sp.lbfgs_mem;
   double* sroad = smem;
-  double* sbox = smem + (a.ra.in_smem ? a.ra.R * d.S * 2 : 0);  // lb[n], ub[n]
+  double* sbox = smem + (a.ra.in_smem ? a.ra.R * road_smem_doubles(d.S) : 0);  // lb[n], ub[n]
   fm_load_smem();
   if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
   for (int i = threadIdx.x; i < n; i += blockDim.x) { sbox[i] = a.lb[i]; sbox[n + i] = a.ub[i]; }
@@ -135,7 +135,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   unsigned long long mask0 = 0, mask1 = 0;  // inactive-set bitmask (n <= 128)
   auto mbit = [&](int j) { return j < 64 ? (mask0 >> j) & 1ull : (mask1 >> (j - 64)) & 1ull; };
   // ---- per-lane registers (this lane's candidate / evaluation request) ----
-  int want = 0, n_val = 0, n_grad = 0;
+  int want = 0, n_val = 0, n_grad = 0, t_rounds = 0, dbg_fd = 0, dbg_lemma = 0, dbg_slide = 0;
   Vec evp{nullptr, 0}, evg{nullptr, 0};
   double val = 0;
   bool c_valid = false, c_pend = false, c_rq = false, c_fb = false, c_acc = false, c_started = false, fd_done = false;
@@ -261,9 +261,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       a.status[b] = fin_status;
       a.iters[2 * b] = alm_i + 1; a.iters[2 * b + 1] = inner_total;
       a.evals[2 * b] = nv; a.evals[2 * b + 1] = ng;
-      a.psi[b] = ppsi; a.res[b] = peps;
+      // MPCB_DEBUG_TIMERS=3: psi carries the instance's evaluation rounds + 1e4 non-speculated FD rounds + 1e8 descent-lemma
+      // re-evaluations at x+ + 1e12 window slides
+      a.psi[b] = d.debug >= 3 ? (double)t_rounds + 1e4 * dbg_fd + 1e8 * dbg_lemma + 1e12 * dbg_slide : ppsi;
+      a.res[b] = peps;
     }
-    n_val = 0; n_grad = 0;
+    n_val = 0; n_grad = 0; t_rounds = 0; dbg_fd = 0; dbg_lemma = 0; dbg_slide = 0;
   };
 
   long long t_eval = 0, t_trans = 0, n_rounds = 0, n_grounds = 0, t_mark = clock64();
@@ -413,6 +416,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
             evp = XE; evg = WL(M.G(cb ^ 1), 0); want = 2;
           }
           ge_row = M.G(cb ^ 1); ge_lane = 0;
+          ++dbg_fd;
           state = ST_FD_DONE;
           break;
         }
@@ -447,27 +451,49 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         // One decision step of the line search (Appendix A 3d), run after every evaluation round.
         const int nb = cb ^ 1;
         const double thr = (1.0 + fabs(phi)) * sp.ls_tol;
+        // phi_gamma(x+) = psi + min_z {g'(z - x+) + |z - x+|^2 / (2 gamma)} can only grow when the descent
+        // lemma shrinks gamma, so a candidate that fails the line-search test with its current gamma fails
+        // it for every smaller gamma: it is rejected at once, without evaluating psi(x̂+) or finishing its
+        // descent-lemma loop — the decision sequential back-tracking reaches at the end of that loop.  The
+        // guard covers the rounding of the two gamma-dependent terms (40-term dot products) and of the
+        // two additions; inside it the candidate is evaluated in full.  NaN fails (as in the sequential test).
+        auto ls_hopeless = [&]() {
+          const double s2 = pTp_n / (2.0 * gam_n);
+          const double lc = psi_n + s2 + gTp_n - (phi - sigma);
+          const double guard = 8.9e-16 * (1.0 + fabs(phi) + fabs(psi_n)) + 1e-12 * (fabs(gTp_n) + s2);
+          return !(lc <= thr + guard);
+        };
+        // After a prox step at (L_n, gam_n): consume every descent-lemma step whose outcome needs no
+        // evaluation.  With psi >= 0 (KDesc.psi_nonneg) the lemma test psi(x̂+) - psi+ > g'p + L/2 |p|^2 + margin
+        // is certainly violated when it is violated for psi(x̂+) = 0 — a back-tracking trial that landed
+        // where psi is huge halves gamma a dozen times before anything else can happen, and none of those
+        // halvings depends on psi(x̂+).  (Sequential back-tracking evaluates psi(x̂+) each time and reaches
+        // the same (L_n, gam_n); the one difference: a NaN psi(x̂+) would have stopped its loop.)
+        auto ls_settle = [&]() {
+          for (;;) {
+            if (!c_fb && ls_hopeless()) { c_pend = false; c_acc = false; return; }
+            const double margin = (1.0 + fabs(psi_n)) * sp.quad_tol;
+            if (!(d.psi_nonneg && 0.0 - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max)) return;
+            L_n *= 2.0; gam_n *= 0.5;
+            prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
+          }
+        };
         if (c_valid && c_pend) {
           if (c_needg) {  // psi, grad psi of this lane's candidate arrived: x̂+, p+ and the tentative phi+
             c_needg = false;
             psi_n = val; L_n = L; gam_n = gam;
             prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
             c_started = true; fd_done = false;
-            if (!c_fb) {
-              // phi_gamma(x+) = psi + min_z {g'(z - x+) + |z - x+|^2 / (2 gamma)} can only grow when the
-              // descent lemma shrinks gamma, so a candidate that fails the line-search test with the
-              // iterate's gamma (beyond a 1e-10 rounding guard) fails it for every smaller gamma: it is
-              // rejected here, without evaluating psi(x̂+).  NaN fails (same as the sequential test).
-              const double lc = psi_n + pTp_n / (2.0 * gam_n) + gTp_n - (phi - sigma);
-              if (!(lc <= thr + 1e-10 * (1.0 + fabs(phi)))) { c_pend = false; c_acc = false; }
-            }
+            ls_settle();
           } else if (c_rq) {  // psi(x̂+) arrived: descent lemma at x+, then the line-search test
             psi_hat_n = val;
             const double margin = (1.0 + fabs(psi_n)) * sp.quad_tol;
             if (psi_hat_n - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max) {
               L_n *= 2.0; gam_n *= 0.5;  // shrink this candidate's step and re-evaluate
+              ++dbg_lemma;
               prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
               fd_done = false;
+              ls_settle();
             } else {
               c_pend = false;
               phi_n = psi_n + pTp_n / (2.0 * gam_n) + gTp_n;
@@ -491,7 +517,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
             if (!c_pend) { ++lsw; ls_assign(false); }
           } else {
             if (slide) {
-              ++lsw;
+              ++lsw; ++dbg_slide;
               ls_assign(false);
               // speculations made for the window's previous candidates are void
               if (spec_for >= 0 && spec_for < G - 1) { fd_done = false; spec_for = -1; }
@@ -587,6 +613,13 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           fd_ready = G >= 2 && fdm != 0 && gam_w == gam;
           fd_lane = fdm ? __ffs(fdm) - 1 : 0;
         }
+        if (d.debug >= 16 && b == d.debug - 16) {  // MPCB_DEBUG_TIMERS=16+i: trace of instance i
+          const int cw = __shfl_sync(tmask, c_idx, tbase + jw);
+          const double gw = tbcast(gam_n, jw), pw = tbcast(pTp_n, jw);
+          if (l == 0)
+            printf("[trace] outer %d k %d rounds %d accepted c=%d lane %d window %d gamma %s fd_ready %d pTp %.3e\n", alm_i, k,
+                   t_rounds, cw, jw, lsw, gw == gam ? "same" : "halved", (int)fd_ready, pw);
+        }
         psi = tbcast(psi_n, jw); psi_hat = tbcast(psi_hat_n, jw);
         gTp = tbcast(gTp_n, jw); pTp = tbcast(pTp_n, jw);
         L = tbcast(L_n, jw); gam = tbcast(gam_n, jw);
@@ -672,6 +705,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     if (!__any_sync(0xffffffffu, want != 0)) break;
     const bool anyg = __any_sync(0xffffffffu, want == 2);
     { long long t = clock64(); t_trans += t - t_mark; t_mark = t; }
+    if (__ballot_sync(0xffffffffu, want != 0) & tmask) ++t_rounds;
     if (want) {
       RoadView r = road_view(a.ra, sroad, d.S, b);
       Extras ex{a.obs ? a.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? a.lam + b * m : nullptr,
