@@ -28,6 +28,16 @@ struct MpcHandle {
   int warps_per_sm = 8;                                // MPCB_WARPS_PER_SM env (experiments)
   int tile_override = 0;                               // MPCB_TILE env: force the lanes-per-instance width
   int last_tile = 0;
+  int mode_override = -1;                              // MPCB_MODE env: 0 persistent kernel, 1 rounds
+  int last_mode = 0;
+  int64_t last_rounds = 0;
+  // round mode (k_solve<..., true> + k_eval_requests): saved lane state, requests, lists, counters
+  double* rs_d = nullptr; size_t rs_d_cap = 0;
+  int32_t* rs_i = nullptr; size_t rs_i_cap = 0;
+  void* rs_req = nullptr; size_t rs_req_cap = 0;
+  double* rs_escr = nullptr; size_t rs_escr_cap = 0;
+  unsigned* rs_counters = nullptr;                     // [8] device
+  unsigned* rs_counters_host = nullptr;                // [4] pinned
   unsigned long long* queue = nullptr;
   double* zero_lam = nullptr; size_t zero_lam_cap = 0;
   // staging for *_host entry points
@@ -204,6 +214,10 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
   if (cudaEventCreateWithFlags(&h->last_ev, cudaEventDisableTiming) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
   if (const char* e = std::getenv("MPCB_DEBUG_TIMERS")) h->debug_timers = std::atoi(e);
   if (const char* e = std::getenv("MPCB_WARPS_PER_SM")) { int w = std::atoi(e); if (w >= 1 && w <= 8) h->warps_per_sm = w; }
+  if (const char* e = std::getenv("MPCB_MODE")) {
+    if (!std::strcmp(e, "rounds") || !std::strcmp(e, "1")) h->mode_override = 1;
+    else if (!std::strcmp(e, "persistent") || !std::strcmp(e, "0")) h->mode_override = 0;
+  }
   if (const char* e = std::getenv("MPCB_TILE")) {
     int g = std::atoi(e);
     if (g == 1 || g == 2 || g == 4 || g == 8) h->tile_override = g;
@@ -215,6 +229,8 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
   cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
+  cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_counters);
+  if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   if (h->pin) cudaFreeHost(h->pin);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   if (h->last_ev) cudaEventDestroy(h->last_ev);
@@ -353,32 +369,121 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   RoadArg ra; size_t smem;
   if ((rc = prepare_road(h, B, road, road_idx, st, &ra, &smem))) return rc;
   smem += (size_t)2 * k.n * sizeof(double);
-  // Tile width: the solve is latency-bound, so spare lanes are spent on speculative line-search
-  // candidates (mpcb_solve.cuh).  255-register lanes: 8 warps per SM resident.
+  // Two execution modes (same state machine, same iterates):
+  //  * persistent (k_solve<.., false>): one launch, tiles pull instances from a queue and evaluate in place;
+  //  * rounds (k_solve<.., true> + k_eval_requests): every round is a transition launch that publishes each
+  //    lane's evaluation request and an evaluation launch over the compacted request lists.  The host
+  //    enqueues rounds ahead of the GPU and reads the request counters every few dozen rounds to stop.
+  // Tile width: spare lanes are spent on speculative line-search candidates (mpcb_solve.cuh).
   const int block = 64;
+  const int mode = h->mode_override >= 0 ? h->mode_override : 1;
   const int64_t lane_cap = (int64_t)h->num_sms * h->warps_per_sm * 32;
   int G = 1;
-  for (int g : {8, 4, 2}) if (B * g <= (int64_t)h->num_sms * 8 * 32) { G = g; break; }
+  if (mode == 1) {
+    // rounds: idle lanes cost nothing in the evaluation launch; speculation pays until the evaluation launch
+    // is throughput-bound (about 4 requests per evaluating lane in flight)
+    G = B <= 8192 ? 8 : (B <= 16384 ? 4 : (B <= 32768 ? 2 : 1));
+  } else {
+    for (int g : {8, 4, 2}) if (B * g <= (int64_t)h->num_sms * 8 * 32) { G = g; break; }
+  }
   if (h->tile_override > 0) G = h->tile_override;
   int64_t tiles_wanted = B;
   int64_t blocks = (tiles_wanted * G + block - 1) / block;
   const int64_t max_blocks = lane_cap / block;
-  if (blocks > max_blocks) blocks = max_blocks;
+  if (mode == 0 && blocks > max_blocks) blocks = max_blocks;
   const int64_t ns = blocks * block, nt = ns / G;
   const bool bounded = k.bounded != 0;
   const int stage_doubles = k.model_id == MPCB_MODEL_PACEJKA6 ? fm_stage_doubles<MPCB_MODEL_PACEJKA6>()
                                                               : fm_stage_doubles<MPCB_MODEL_KINEMATIC4>();
-  LaneMap LM(k.n, k.N, k.nx, stage_doubles, bounded);
+  LaneMap LM(k.n, k.N, k.nx, mode == 1 ? 0 : stage_doubles, bounded);
   TileMap TM(k.n, G, sp->lbfgs_mem, k.m, bounded);
   if ((rc = grow(h, &h->ws, &h->ws_cap, (size_t)LM.total * ns * sizeof(double), st))) return rc;
   if ((rc = grow(h, &h->wst, &h->wst_cap, (size_t)TM.total * nt * sizeof(double), st))) return rc;
   CK(cudaMemsetAsync(h->queue, 0, sizeof(unsigned long long), st));
   SolveArgs a;
+  std::memset(&a, 0, sizeof(a));
   a.B = B; a.x0 = x0; a.p = p; a.obs = obs; a.lb = lb; a.ub = ub; a.ra = ra; a.U = U; a.lam = lambda;
   a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res;
   a.ws = h->ws; a.wst = h->wst; a.ns = ns; a.nt = nt; a.queue = h->queue;
   a.dbg = nullptr;
   h->kd.debug = h->debug_timers;
+  h->last_tile = G;
+  h->last_mode = mode;
+  if (mode == 1) {
+    const size_t box_smem = (size_t)2 * k.n * sizeof(double);
+    const size_t road_smem = smem - box_smem;
+    // evaluation launch: 2 CTAs of 128 lanes per SM (255-register lanes), never more lanes than requests can exist
+    int64_t eblocks = (ns + 127) / 128;
+    if (eblocks > (int64_t)h->num_sms * 2) eblocks = (int64_t)h->num_sms * 2;
+    const int64_t ens = eblocks * 128;
+    if ((rc = grow(h, &h->rs_d, &h->rs_d_cap, (size_t)MPCB_SD_ROWS * ns * sizeof(double), st))) return rc;
+    if ((rc = grow(h, &h->rs_i, &h->rs_i_cap, (size_t)MPCB_SI_ROWS * ns * sizeof(int32_t), st))) return rc;
+    // requests: want[ns] i32, list_grad[ns] i32, list_val[ns] i32, (pad) b[ns] i64, p[ns], g[ns] ptr, val[ns] f64
+    const size_t ns8 = ((size_t)ns + 1) & ~size_t(1);
+    if ((rc = grow(h, (char**)&h->rs_req, &h->rs_req_cap, ns8 * (3 * 4 + 4 * 8) + 64, st))) return rc;
+    if ((rc = grow(h, &h->rs_escr, &h->rs_escr_cap, (size_t)k.N * stage_doubles * ens * sizeof(double), st))) return rc;
+    if (!h->rs_counters) {
+      CK(cudaMalloc((void**)&h->rs_counters, 8 * sizeof(unsigned)));
+      CK(cudaMallocHost((void**)&h->rs_counters_host, 4 * sizeof(unsigned)));
+    }
+    CK(cudaMemsetAsync(h->rs_counters, 0, 8 * sizeof(unsigned), st));
+    char* rq = (char*)h->rs_req;
+    a.req_b = (int64_t*)rq;
+    a.req_p = (double**)(rq + ns8 * 8);
+    a.req_g = (double**)(rq + ns8 * 16);
+    a.req_val = (double*)(rq + ns8 * 24);
+    a.req_want = (int32_t*)(rq + ns8 * 32);
+    a.list_grad = (int32_t*)(rq + ns8 * 36);
+    a.list_val = (int32_t*)(rq + ns8 * 40);
+    a.sd = h->rs_d; a.si = h->rs_i; a.counters = h->rs_counters;
+    EvalArgs e;
+    std::memset(&e, 0, sizeof(e));
+    e.ns = ns; e.nt = nt; e.ens = ens; e.G = G;
+    e.x0 = x0; e.p = p; e.obs = obs; e.lam = lambda; e.sig_base = h->wst + (size_t)TM.SIG * nt; e.ra = ra;
+    e.req_want = a.req_want; e.req_b = a.req_b; e.req_p = a.req_p; e.req_g = a.req_g; e.req_val = a.req_val;
+    e.list_grad = a.list_grad; e.list_val = a.list_val; e.escr = h->rs_escr;
+#define MPCB_LAUNCH_T(MODEL, GG)                                                               \
+  do {                                                                                         \
+    k_solve<MODEL, GG, true><<<(unsigned)blocks, block, box_smem, st>>>(k, *sp, a);            \
+  } while (0)
+#define MPCB_LAUNCH_T_G(MODEL)                                                                 \
+  switch (G) {                                                                                 \
+    case 8: MPCB_LAUNCH_T(MODEL, 8); break;                                                    \
+    case 4: MPCB_LAUNCH_T(MODEL, 4); break;                                                    \
+    case 2: MPCB_LAUNCH_T(MODEL, 2); break;                                                    \
+    default: MPCB_LAUNCH_T(MODEL, 1); break;                                                   \
+  }
+    if (k.model_id == MPCB_MODEL_PACEJKA6) { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_PACEJKA6>, road_smem))) return rc; }
+    else { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_KINEMATIC4>, road_smem))) return rc; }
+    int64_t round = 0;
+    const int64_t round_cap = 4000000;
+    int chunk = 48;
+    for (;;) {
+      for (int i = 0; i < chunk; ++i, ++round) {
+        a.round = (int)round;
+        e.counters = h->rs_counters + 4 * (round & 1);
+        if (k.model_id == MPCB_MODEL_PACEJKA6) {
+          MPCB_LAUNCH_T_G(MPCB_MODEL_PACEJKA6)
+          k_eval_requests<MPCB_MODEL_PACEJKA6><<<(unsigned)eblocks, 128, road_smem, st>>>(k, e);
+        } else {
+          MPCB_LAUNCH_T_G(MPCB_MODEL_KINEMATIC4)
+          k_eval_requests<MPCB_MODEL_KINEMATIC4><<<(unsigned)eblocks, 128, road_smem, st>>>(k, e);
+        }
+      }
+      h->launches += 2 * chunk;
+      CK(cudaGetLastError());
+      CK(cudaMemcpyAsync(h->rs_counters_host, h->rs_counters + 4 * ((round - 1) & 1), 4 * sizeof(unsigned),
+                         cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      if (h->rs_counters_host[0] == 0 && h->rs_counters_host[1] == 0) break;
+      if (round > round_cap) return fail(h, MPCB_E_CUDA, "mpcb_solve: round cap exceeded");
+      chunk = 24;
+    }
+#undef MPCB_LAUNCH_T_G
+#undef MPCB_LAUNCH_T
+    h->last_rounds = round;
+    return leave(h, st);
+  }
   if (h->debug_timers) {
     unsigned long long z[2] = {0, 0};
     CK(cudaMemcpyToSymbolAsync(g_dbg_calls, z, sizeof(z), 0, cudaMemcpyHostToDevice, st));
@@ -389,8 +494,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   }
 #define MPCB_LAUNCH_SOLVE(MODEL, GG)                                                           \
   do {                                                                                         \
-    if ((rc = set_smem(h, k_solve<MODEL, GG>, smem))) return rc;                               \
-    k_solve<MODEL, GG><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);                      \
+    if ((rc = set_smem(h, k_solve<MODEL, GG, false>, smem))) return rc;                        \
+    k_solve<MODEL, GG, false><<<(unsigned)blocks, block, smem, st>>>(k, *sp, a);               \
   } while (0)
 #define MPCB_LAUNCH_SOLVE_G(MODEL)                                                             \
   switch (G) {                                                                                 \

@@ -49,7 +49,20 @@ struct SolveArgs {
   int64_t ns, nt;
   unsigned long long* queue;
   long long* dbg;  // optional [warps, 4]: cycles in evaluation / transition phases, rounds, gradient rounds
+  // ---- round mode (k_solve<.., ROUND = true> + k_eval_requests, see below) ----
+  int round;                 // index of this transition launch
+  double* sd;                // saved lane state, doubles  [MPCB_SD_ROWS, ns]
+  int32_t* si;               // saved lane state, ints     [MPCB_SI_ROWS, ns]
+  int32_t* req_want;         // [ns] evaluation request of every lane: 0 none, 1 psi, 2 psi + grad psi, 3 psi + states
+  int64_t* req_b;            // [ns] instance
+  double** req_p;            // [ns] point to evaluate (lane-interleaved row, stride ns)
+  double** req_g;            // [ns] gradient row (want 2) / state row (want 3)
+  double* req_val;           // [ns] psi written by the evaluation kernel
+  int32_t* list_grad;        // compacted lanes whose request wants a gradient
+  int32_t* list_val;         // compacted lanes whose request wants psi only
+  unsigned* counters;        // [2][4] by round parity: gradient requests, value requests, evaluation work counter
 };
+constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 25;
 
 enum SolveState {
   ST_IDLE = 0, ST_START_PANOC, ST_INIT_G1, ST_LIP_DONE, ST_XHAT_REQ, ST_XHAT_DONE, ST_ITER_TOP, ST_FD_DONE,
@@ -79,19 +92,22 @@ struct TileMap {
   }
 };
 
-template <int MODEL, int G>
+template <int MODEL, int G, bool ROUND>
 __global__ void __launch_bounds__(64)
 k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   constexpr int NX = Fm<MODEL>::NX;
-  constexpr int K = fm_stage_doubles<MODEL>();
+  constexpr int K = ROUND ? 0 : fm_stage_doubles<MODEL>();  // round mode: the stage Jacobians live in the evaluation kernel's scratch
   extern __shared__ double smem[];
   const int n = d.n, m = d.m, mem = sp.lbfgs_mem;
   double* sroad = smem;
-  double* sbox = smem + (a.ra.in_smem ? a.ra.R * road_smem_doubles(d.S) : 0);  // lb[n], ub[n]
-  fm_load_smem();
-  if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
+  double* sbox = smem + (!ROUND && a.ra.in_smem ? a.ra.R * road_smem_doubles(d.S) : 0);  // lb[n], ub[n]
+  if constexpr (!ROUND) {
+    fm_load_smem();
+    if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
+  }
   for (int i = threadIdx.x; i < n; i += blockDim.x) { sbox[i] = a.lb[i]; sbox[n + i] = a.ub[i]; }
-  stage_problem(d, a.p);
+  if constexpr (ROUND) __syncthreads();
+  else stage_problem(d, a.p);
   const double* lbv = sbox;
   const double* ubv = sbox + n;
 
@@ -142,6 +158,37 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   bool c_needg = false;
   int c_idx = 0, spec_for = -1;
   double psi_n = 0, psi_hat_n = 0, gTp_n = 0, pTp_n = 0, L_n = 0, gam_n = 0, phi_n = 0;
+
+  // ---- round mode: the registers above live in global memory between transition launches ----
+#define MPCB_STATE_D(X) X(psi) X(psi_hat) X(gTp) X(pTp) X(L) X(gam) X(phi) X(tau0) X(sigma) X(hfd) X(hh) X(eps_tol) X(peps) \
+  X(ppsi) X(norm_e2) X(psi_n) X(psi_hat_n) X(gTp_n) X(pTp_n) X(L_n) X(gam_n) X(phi_n)
+#define MPCB_STATE_I(X) X(state) X(cl) X(cb) X(fd_lane) X(ge_row) X(ge_lane) X(k) X(no_prog) X(lb_idx) X(lb_full) X(hb) X(lsw) \
+  X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for)
+  bool dead = false;  // round mode: this tile has no instance left
+  if constexpr (ROUND) {
+    if (a.round > 0) {
+      const int fl = a.si[slot];
+      exhausted = fl & 1; fd_ready = fl & 2; c_valid = fl & 4; c_pend = fl & 8; c_rq = fl & 16; c_fb = fl & 32;
+      c_acc = fl & 64; c_started = fl & 128; fd_done = fl & 256; c_needg = fl & 512;
+      dead = fl & 1024;
+      if (!dead) {
+        int r = 1;
+#define X(v) v = a.si[(int64_t)(r++) * ns + slot];
+        MPCB_STATE_I(X)
+#undef X
+        specmask = (unsigned)a.si[(int64_t)(r++) * ns + slot];
+        r = 0;
+#define X(v) v = a.sd[(int64_t)(r++) * ns + slot];
+        MPCB_STATE_D(X)
+#undef X
+        mask0 = (unsigned long long)__double_as_longlong(a.sd[(int64_t)(r++) * ns + slot]);
+        mask1 = (unsigned long long)__double_as_longlong(a.sd[(int64_t)(r++) * ns + slot]);
+        b = __double_as_longlong(a.sd[(int64_t)(r++) * ns + slot]);
+        val = a.req_val[slot];
+      }
+    }
+  }
+  const bool was_dead = dead;
 
   // x̂ = Π_C(x − γ g), p = x̂ − x (stored into XH, P); returns gᵀp and pᵀp
   auto prox = [&](const Vec& X, const Vec& Gv, double gamma, const Vec& XH, const Vec& P, double& gtp, double& ptp) {
@@ -273,7 +320,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   for (;;) {
     // ================= transition phase: run the tile's state machine up to its next evaluation ====
     want = 0;
-    for (;;) {
+    for (; !dead;) {
       if (state == ST_IDLE) {
         if (exhausted) break;
         long long bb = 0;
@@ -701,6 +748,54 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         state = ST_START_PANOC;
       }
     }
+    if constexpr (ROUND) {
+      // ================= round mode: publish the request, save the registers, leave ===============
+      // (the evaluation runs in k_eval_requests over the compacted request lists)
+      unsigned* cnt = a.counters + 4 * (a.round & 1);
+      if (slot == 0) {  // the other parity's counters: last read by the previous evaluation launch
+        unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
+        nx[0] = 0u; nx[1] = 0u; nx[2] = 0u;
+      }
+      if (!dead) {
+        if (__ballot_sync(tmask, want != 0) & tmask) ++t_rounds;
+        if (exhausted && state == ST_IDLE) dead = true;
+      }
+      const unsigned mg = __ballot_sync(0xffffffffu, want == 2);
+      const unsigned mv = __ballot_sync(0xffffffffu, want == 1 || want == 3);
+      unsigned bg = 0, bv = 0;
+      if (lane == 0) {
+        if (mg) bg = atomicAdd(&cnt[0], (unsigned)__popc(mg));
+        if (mv) bv = atomicAdd(&cnt[1], (unsigned)__popc(mv));
+      }
+      bg = __shfl_sync(0xffffffffu, bg, 0);
+      bv = __shfl_sync(0xffffffffu, bv, 0);
+      const unsigned below_me = (1u << lane) - 1u;
+      if (want) {
+        a.req_want[slot] = want; a.req_b[slot] = b; a.req_p[slot] = evp.p;
+        a.req_g[slot] = want == 3 ? WL(M.ST, l).p : evg.p;
+        if (want == 2) { a.list_grad[bg + __popc(mg & below_me)] = (int32_t)slot; ++n_grad; }
+        else { a.list_val[bv + __popc(mv & below_me)] = (int32_t)slot; if (want == 1) ++n_val; }
+      }
+      if (!was_dead) {  // tiles that were already dead keep their saved flags
+        a.si[slot] = (int)exhausted | (int)fd_ready << 1 | (int)c_valid << 2 | (int)c_pend << 3 | (int)c_rq << 4 | (int)c_fb << 5 |
+                     (int)c_acc << 6 | (int)c_started << 7 | (int)fd_done << 8 | (int)c_needg << 9 | (int)dead << 10;
+        if (!dead) {
+          int r = 1;
+#define X(v) a.si[(int64_t)(r++) * ns + slot] = v;
+          MPCB_STATE_I(X)
+#undef X
+          a.si[(int64_t)(r++) * ns + slot] = (int)specmask;
+          r = 0;
+#define X(v) a.sd[(int64_t)(r++) * ns + slot] = v;
+          MPCB_STATE_D(X)
+#undef X
+          a.sd[(int64_t)(r++) * ns + slot] = __longlong_as_double((long long)mask0);
+          a.sd[(int64_t)(r++) * ns + slot] = __longlong_as_double((long long)mask1);
+          a.sd[(int64_t)(r++) * ns + slot] = __longlong_as_double((long long)b);
+        }
+      }
+      return;
+    } else {
     // ================= evaluation phase: the one convergent site ================================
     if (!__any_sync(0xffffffffu, want != 0)) break;
     const bool anyg = __any_sync(0xffffffffu, want == 2);
@@ -722,10 +817,76 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     }
     __syncwarp();
     { long long t = clock64(); t_eval += t - t_mark; t_mark = t; ++n_rounds; n_grounds += anyg; }
+    }
   }
   if (a.dbg && lane == 0) {
     long long* o = a.dbg + 4 * (slot >> 5);
     o[0] = t_eval; o[1] = t_trans; o[2] = n_rounds; o[3] = n_grounds;
+  }
+}
+
+// ---- round mode: evaluation of the published requests -------------------------------------------------
+// One launch per round, after the transition launch.  Warps pull chunks of 32 requests from the two
+// compacted lists (gradient requests first, then psi-only requests), so every warp runs ONE variant of
+// the evaluation with all its lanes busy, whatever PANOC iteration the owning tiles are in, and the
+// requests of the few instances still running at the end of a batch spread over the whole GPU.  Only the
+// evaluation code is resident (the transition kernel's 400 KB never compete for the instruction cache).
+struct EvalArgs {
+  int64_t ns, nt, ens;
+  int G;
+  const double *x0, *p, *obs, *lam;
+  const double* sig_base;   // ALM penalties: sig_base[r * nt + tile]
+  RoadArg ra;
+  const int32_t* req_want;
+  const int64_t* req_b;
+  double* const* req_p;
+  double* const* req_g;
+  double* req_val;
+  const int32_t *list_grad, *list_val;
+  unsigned* counters;       // this round's [4]
+  double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
+};
+
+template <int MODEL>
+__global__ void __launch_bounds__(128)
+k_eval_requests(KDesc d, EvalArgs e) {
+  constexpr int NX = Fm<MODEL>::NX;
+  extern __shared__ double smem[];
+  double* sroad = smem;
+  fm_load_smem();
+  if (e.ra.in_smem) stage_roads(sroad, e.ra.road, e.ra.R, d.S);
+  stage_problem(d, e.p);
+  const int lane = threadIdx.x & 31;
+  const int64_t eslot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const Vec scr{e.escr + eslot, e.ens};
+  const unsigned ng = e.counters[0], nv = e.counters[1];
+  const unsigned cg = (ng + 31u) >> 5, cv = (nv + 31u) >> 5;
+  for (;;) {
+    unsigned c = 0;
+    if (lane == 0) c = atomicAdd(&e.counters[2], 1u);
+    c = __shfl_sync(0xffffffffu, c, 0);
+    if (c >= cg + cv) break;
+    const bool grad = c < cg;
+    const unsigned idx = ((grad ? c : c - cg) << 5) + (unsigned)lane;
+    if (idx < (grad ? ng : nv)) {
+      const int64_t slot = grad ? e.list_grad[idx] : e.list_val[idx];
+      const int want = e.req_want[slot];
+      const int64_t b = e.req_b[slot];
+      const int64_t tile = slot / e.G;
+      RoadView r = road_view(e.ra, sroad, d.S, b);
+      Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
+                d.bounded ? e.sig_base + tile : nullptr, 1, e.nt};
+      double y0[NX];
+#pragma unroll
+      for (int i = 0; i < NX; ++i) y0[i] = e.x0[b * NX + i];
+      const Vec pt{e.req_p[slot], e.ns};
+      const Vec out{e.req_g[slot], e.ns};
+      double v;
+      if (grad) v = eval_fm<MODEL, true>(r, ex, y0, pt, scr, out, true, Vec{nullptr, 0});
+      else v = eval_fm<MODEL, false>(r, ex, y0, pt, scr, Vec{nullptr, 0}, false, want == 3 ? out : Vec{nullptr, 0});
+      e.req_val[slot] = v;
+    }
+    __syncwarp();
   }
 }
 

@@ -241,6 +241,35 @@ def test_every_tile_width_tracks_oracle(mp, orc, G, monkeypatch):
     assert abs(gi.mean() - r["inner"].mean()) < 0.03 * r["inner"].mean()
 
 
+@pytest.mark.parametrize("G", [8, 2, 1])
+@pytest.mark.parametrize("bounded", [False, True])
+def test_round_mode_equals_persistent_mode(mp, G, bounded, monkeypatch):
+    """The two execution modes of mpcb_solve (one persistent kernel / transition + evaluation launches per
+    round, MPCB_MODE) run the same state machine on the same evaluations: bit-identical iterates, statuses,
+    iteration and evaluation counts, multipliers."""
+    from mpcb200 import workloads as wl
+    N, B, S = 12, 150, 100
+    w = wl.tracking_batch(B, N, S, seed=31)
+    out = {}
+    for mode in ("persistent", "rounds"):
+        monkeypatch.setenv("MPCB_MODE", mode)
+        monkeypatch.setenv("MPCB_TILE", str(G))
+        kw = {}
+        if bounded:  # main.py:46-51 state constraints with D = (-inf, 0]
+            kw = dict(flags=mp.FLAG_BOUNDED_D, D_lower=[-np.inf] * 6, D_upper=[0.0] * 6)
+        prob = mp.BatchedMpc(N=N, S=S, road_mode=mp.ROAD_TABLE, n_roads=2, **kw)
+        lam = np.zeros((B, 6 * N)) if bounded else None
+        U, lam_o, st = prob.solve(w["x0"], w["road"], w["U0"].copy(), lam=lam, road_idx=w["road_idx"])
+        out[mode] = (U.cpu().numpy(), None if lam_o is None else lam_o.cpu().numpy(), st)
+    (U0, l0, s0), (U1, l1, s1) = out["persistent"], out["rounds"]
+    assert (U0 == U1).all()
+    if bounded:
+        assert (l0 == l1).all()
+    for f in ("status", "outer_iterations", "inner_iterations", "evals_value", "evals_grad", "psi", "residual"):
+        a, b = getattr(s0, f).cpu().numpy(), getattr(s1, f).cpu().numpy()
+        assert ((a == b) | (np.isnan(a) & np.isnan(b))).all(), f
+
+
 def test_solve_host_equals_solve_device(mp, orc):
     from mpcb200 import workloads as wl
     N, B = 12, 100
