@@ -4,15 +4,19 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--batch B] [--horizon N]
 
 Step = one pass of the hot path over one batch: cold-start ALM/PANOC solve of `batch` independent N=20
-tracking MPCs per GPU (BASELINE config 2: 4096 instances, Pacejka-6, S=100, 2-road table; weak scaling:
-every rank solves its own `batch` instances, no data-path collective).
+tracking MPCs per GPU.  The instances follow BASELINE config 2's recipe (Pacejka-6, S=100, 2-road table, random
+initial states); the batch is the one BASELINE.json's metric is quoted on ("N=20, batch 64K": 65536 per GPU, it
+fits one GPU).  Weak scaling: every rank solves its own `batch` instances, no data-path collective.  Config 2
+itself (4096 instances) is measured next to it and reported under "config2_b4096".
 
-  value    : solves/s with inputs resident in HBM (one k_solve launch per step, CUDA-event timed, max over ranks)
+  value    : solves/s with inputs resident in HBM (one mpcb_solve call per step, CUDA-event timed, max over ranks)
   e2e      : solves/s through the reference-facing host call (numpy buffers -> mpcb_solve_host: pinned
              staging + H2D + solve + D2H inside the timed region)
-  roofline : FP64-pipe roofline of k_solve: algorithmic flops (SURVEY §8d strict count, 3864*N per psi+grad
-             evaluation, 0.455 of that per psi-only evaluation, times the kernel's own evaluation counters)
-             / event time, against the DFMA-chain peak measured in this run (MEASURED_PEAKS.json has no FP64 entry)
+  roofline : FP64-pipe roofline of the dominant kernel (round mode: k_eval_requests, one launch per round;
+             persistent mode: k_solve): algorithmic flops (SURVEY §8d strict count, 3864*N per psi+grad
+             evaluation, 0.455 of that per psi-only evaluation, times the kernels' own evaluation counters)
+             / the kernel's launch durations (CUDA events on the launch stream, inside the timed region),
+             against the DFMA-chain peak measured in this run (MEASURED_PEAKS.json has no FP64 entry)
   cpu_baseline : the CPU oracle (C++ port of the same spec; alpaqa/CasADi cannot be installed) on a bounded
              sample of the same workload, all host threads.
 --impl reference times that oracle as the reference arm.
@@ -41,7 +45,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="mpcb200", choices=["mpcb200", "reference"])
-    ap.add_argument("--batch", type=int, default=4096, help="instances per GPU")
+    ap.add_argument("--batch", type=int, default=65536, help="instances per GPU")
     ap.add_argument("--horizon", type=int, default=20)
     ap.add_argument("--cpu-sample", type=int, default=0, help="oracle sample size (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -49,7 +53,8 @@ def parse():
 
 
 def workload_name(B, N):
-    return f"config2: {B} independent N={N} Pacejka-6 tracking MPCs per GPU, S=100, 2-road table, cold start"
+    return (f"{B} independent N={N} Pacejka-6 tracking MPCs per GPU (BASELINE metric batch 64K; config-2 instance recipe), "
+            "S=100, 2-road table, cold start")
 
 
 class ClockSampler:
@@ -206,12 +211,14 @@ def main_gpu(args, rank, local_rank, world):
     barrier()
     t_wall0 = time.perf_counter()
     all_stats = []
+    profs = []
     for i in range(K):
         flush.zero_()  # L2 flush between timed iterations (not timed)
         evs[i][0].record()
         _, _, st = prob.solve(x0, road, Ubufs[W + i], road_idx=ridx)
         evs[i][1].record()
         all_stats.append(st)
+        profs.append(prob.last_solve_profile())
     barrier()
     t_wall1 = time.perf_counter()
     launches = prob.launch_count() - l0
@@ -226,12 +233,21 @@ def main_gpu(args, rank, local_rank, world):
     n_grad = float(st.evals_grad.sum().item())
     flop_eval = FLOP_PER_STAGE_GRAD * N
     alg_flops = (n_grad + VALUE_SHARE * n_val) * flop_eval
-    k_ms = float(np.mean(step_ms))
+    prof = profs[-1]
+    rounds_mode = prof["mode"] == "rounds"
+    # dominant kernel: the evaluation launches in round mode (their summed CUDA-event durations), else the one kernel
+    k_ms = float(prof["eval_ms"]) if rounds_mode else float(step_ms[-1])
+    n_k_launches = prof["eval_launches"]
     achieved = alg_flops / (k_ms * 1e-3) / 1e12
     weighted = (n_grad + VALUE_SHARE * n_val) * WEIGHTED_FLOP_PER_EVAL_N20 * (N / 20.0) / (k_ms * 1e-3) / 1e12
     alg_bytes = B * (6 * 8 + 2 * N * 8 * 2 + 4 + 4 * 4 + 2 * 8 + 4 * 4)  # x0, U in/out, road_idx, status/iters/evals, psi/res
-    roofline = {"bound": "fp64", "kernel": "k_solve<Pacejka6>", "achieved": achieved, "peak": peak_tflops,
+    roofline = {"bound": "fp64", "kernel": "k_eval_requests<Pacejka6>" if rounds_mode else "k_solve<Pacejka6>",
+                "achieved": achieved, "peak": peak_tflops,
                 "unit": "TFLOP/s", "frac": achieved / peak_tflops, "traffic": None,
+                "launches_per_step": n_k_launches, "avg_launch_ms": k_ms / max(n_k_launches, 1),
+                "flop_per_launch": alg_flops / max(n_k_launches, 1),
+                "kernel_share_of_step": k_ms / float(step_ms[-1]),
+                "solve_profile": prof,
                 "peak_source": "DFMA-chain probe measured in this run (mpcb_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
                 "flop_per_eval": flop_eval, "evals_grad_per_step": n_grad, "evals_value_per_step": n_val,
                 "weighted_achieved": weighted, "weighted_frac": weighted / peak_tflops,
@@ -249,7 +265,6 @@ def main_gpu(args, rank, local_rank, world):
     barrier()
     t_e2e = max_over_ranks(t_e2e)
     h2d, d2h = prob.last_transfer_bytes()
-    launches += K
 
     # ---- single-instance latency (the reference's deployment shape: one vehicle, one tick) ------------
     lat1 = []
@@ -262,6 +277,25 @@ def main_gpu(args, rank, local_rank, world):
         torch.cuda.synchronize()
         lat1.append(a.elapsed_time(b))
     conv = sum_over_ranks(float((status == 1).sum())) / (world * B)
+
+    # ---- BASELINE config 2 itself: 4096 instances on one GPU (reported next to the headline) ----------------
+    cfg2 = None
+    if B != 4096:
+        B2 = 4096
+        w2 = wl.tracking_batch(B2, N, S, seed=2 + rank)
+        x2, r2 = torch.tensor(w2["x0"], device=dev), torch.tensor(w2["road_idx"], device=dev)
+        U2 = [torch.tensor(w2["U0"], device=dev) for _ in range(3)]
+        t2 = []
+        for i in range(3):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            _, _, s2 = prob.solve(x2, road, U2[i], road_idx=r2)
+            b.record()
+            torch.cuda.synchronize()
+            t2.append(a.elapsed_time(b))
+        launches += 0  # outside the timed region
+        cfg2 = {"batch": B2, "ms_per_batch": float(np.median(t2[1:])), "solves_per_s": B2 / float(np.median(t2[1:])) * 1e3,
+                "converged_frac": float((s2.status == 1).double().mean().item()), "solve_profile": prob.last_solve_profile()}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -285,6 +319,8 @@ def main_gpu(args, rank, local_rank, world):
                 "e2e": {"value": world * B * K / t_e2e, "unit": "solves/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+        if cfg2:
+            line["config2_b4096"] = cfg2
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)

@@ -199,6 +199,13 @@ int mpcb_latency_probe(double* cycles8);
  * warps written (<= max_warps). */
 int64_t mpcb_debug_timers(MpcHandle* h, long long* out4, int64_t max_warps);
 
+/* Execution profile of the last mpcb_solve on this handle, measured with CUDA events on the launch stream:
+ * out6 = [mode (0 persistent kernel, 1 rounds), tile width G, rounds, evaluation-kernel ms (sum over rounds),
+ * transition-kernel ms (sum over rounds), evaluation launches].  mpcb_solve picks the mode (MPCB_MODE=persistent|rounds
+ * overrides): in round mode the call enqueues transition + evaluation launches round after round and blocks the
+ * host until the batch is done; the persistent mode is one asynchronous launch. */
+void mpcb_last_solve_profile(MpcHandle* h, double* out6);
+
 /* Number of kernels launched through this handle since creation (bench.py's gpu_launches). */
 int64_t mpcb_launch_count(MpcHandle* h);
 

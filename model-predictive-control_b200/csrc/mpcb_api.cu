@@ -31,13 +31,16 @@ struct MpcHandle {
   int mode_override = -1;                              // MPCB_MODE env: 0 persistent kernel, 1 rounds
   int last_mode = 0;
   int64_t last_rounds = 0;
+  double last_eval_ms = 0.0, last_trans_ms = 0.0;
+  cudaEvent_t rs_ev[3 * 64] = {};                      // per-round timing events of one chunk
   // round mode (k_solve<..., true> + k_eval_requests): saved lane state, requests, lists, counters
   double* rs_d = nullptr; size_t rs_d_cap = 0;
   int32_t* rs_i = nullptr; size_t rs_i_cap = 0;
   void* rs_req = nullptr; size_t rs_req_cap = 0;
   double* rs_escr = nullptr; size_t rs_escr_cap = 0;
   unsigned* rs_counters = nullptr;                     // [8] device
-  unsigned* rs_counters_host = nullptr;                // [4] pinned
+  unsigned* rs_counters_host = nullptr;                // [64][4] pinned: every round's request counters of one chunk
+  const char* round_log = nullptr;                     // MPCB_ROUND_LOG=path: per-round [grad requests, psi requests, T ms, E ms]
   unsigned long long* queue = nullptr;
   double* zero_lam = nullptr; size_t zero_lam_cap = 0;
   // staging for *_host entry points
@@ -214,6 +217,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
   if (cudaEventCreateWithFlags(&h->last_ev, cudaEventDisableTiming) != cudaSuccess) { cudaFree(h->queue); delete h; return MPCB_E_CUDA; }
   if (const char* e = std::getenv("MPCB_DEBUG_TIMERS")) h->debug_timers = std::atoi(e);
   if (const char* e = std::getenv("MPCB_WARPS_PER_SM")) { int w = std::atoi(e); if (w >= 1 && w <= 8) h->warps_per_sm = w; }
+  h->round_log = std::getenv("MPCB_ROUND_LOG");
   if (const char* e = std::getenv("MPCB_MODE")) {
     if (!std::strcmp(e, "rounds") || !std::strcmp(e, "1")) h->mode_override = 1;
     else if (!std::strcmp(e, "persistent") || !std::strcmp(e, "0")) h->mode_override = 0;
@@ -231,6 +235,7 @@ void mpcb_destroy(MpcHandle* h) {
   cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
   cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_counters);
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
+  for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
   if (h->pin) cudaFreeHost(h->pin);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   if (h->last_ev) cudaEventDestroy(h->last_ev);
@@ -239,6 +244,11 @@ void mpcb_destroy(MpcHandle* h) {
 
 const char* mpcb_last_error(MpcHandle* h) { return h ? h->err.c_str() : "null handle"; }
 int64_t mpcb_launch_count(MpcHandle* h) { return h ? h->launches : 0; }
+void mpcb_last_solve_profile(MpcHandle* h, double* out) {
+  if (!h || !out) return;
+  out[0] = h->last_mode; out[1] = h->last_tile; out[2] = (double)h->last_rounds;
+  out[3] = h->last_eval_ms; out[4] = h->last_trans_ms; out[5] = h->last_mode ? (double)h->last_rounds : 1.0;
+}
 
 int mpcb_dynamics(MpcHandle* h, int64_t B, const double* x, const double* u, const double* p, int32_t clip,
                   double* out, void* stream) {
@@ -368,7 +378,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   }
   RoadArg ra; size_t smem;
   if ((rc = prepare_road(h, B, road, road_idx, st, &ra, &smem))) return rc;
-  smem += (size_t)2 * k.n * sizeof(double);
+  const size_t road_smem = smem;
   // Two execution modes (same state machine, same iterates):
   //  * persistent (k_solve<.., false>): one launch, tiles pull instances from a queue and evaluate in place;
   //  * rounds (k_solve<.., true> + k_eval_requests): every round is a transition launch that publishes each
@@ -387,6 +397,10 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     for (int g : {8, 4, 2}) if (B * g <= (int64_t)h->num_sms * 8 * 32) { G = g; break; }
   }
   if (h->tile_override > 0) G = h->tile_override;
+  // + box [2n] + the two-loop recursion scalars of the CTA's tiles [64 / G][2 mem]
+  const size_t box_smem = ((size_t)2 * k.n + (size_t)(64 / G) * 2 * sp->lbfgs_mem) * sizeof(double);
+  smem += box_smem;
+  if (smem > 200 * 1024) return fail(h, MPCB_E_UNSUPPORTED, "mpcb_solve: road table + L-BFGS scalars exceed shared memory");
   int64_t tiles_wanted = B;
   int64_t blocks = (tiles_wanted * G + block - 1) / block;
   const int64_t max_blocks = lane_cap / block;
@@ -410,12 +424,10 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   h->last_tile = G;
   h->last_mode = mode;
   if (mode == 1) {
-    const size_t box_smem = (size_t)2 * k.n * sizeof(double);
-    const size_t road_smem = smem - box_smem;
-    // evaluation launch: 2 CTAs of 128 lanes per SM (255-register lanes), never more lanes than requests can exist
-    int64_t eblocks = (ns + 127) / 128;
-    if (eblocks > (int64_t)h->num_sms * 2) eblocks = (int64_t)h->num_sms * 2;
-    const int64_t ens = eblocks * 128;
+    // evaluation launch: one CTA of 256 lanes (255 registers each) per SM, never more lanes than requests can exist
+    int64_t eblocks = (ns + 255) / 256;
+    if (eblocks > (int64_t)h->num_sms) eblocks = (int64_t)h->num_sms;
+    const int64_t ens = eblocks * 256;
     if ((rc = grow(h, &h->rs_d, &h->rs_d_cap, (size_t)MPCB_SD_ROWS * ns * sizeof(double), st))) return rc;
     if ((rc = grow(h, &h->rs_i, &h->rs_i_cap, (size_t)MPCB_SI_ROWS * ns * sizeof(int32_t), st))) return rc;
     // requests: want[ns] i32, list_grad[ns] i32, list_val[ns] i32, (pad) b[ns] i64, p[ns], g[ns] ptr, val[ns] f64
@@ -424,7 +436,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     if ((rc = grow(h, &h->rs_escr, &h->rs_escr_cap, (size_t)k.N * stage_doubles * ens * sizeof(double), st))) return rc;
     if (!h->rs_counters) {
       CK(cudaMalloc((void**)&h->rs_counters, 8 * sizeof(unsigned)));
-      CK(cudaMallocHost((void**)&h->rs_counters_host, 4 * sizeof(unsigned)));
+      CK(cudaMallocHost((void**)&h->rs_counters_host, 64 * 4 * sizeof(unsigned)));
     }
     CK(cudaMemsetAsync(h->rs_counters, 0, 8 * sizeof(unsigned), st));
     char* rq = (char*)h->rs_req;
@@ -444,6 +456,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     e.list_grad = a.list_grad; e.list_val = a.list_val; e.escr = h->rs_escr;
 #define MPCB_LAUNCH_T(MODEL, GG)                                                               \
   do {                                                                                         \
+    if (round == 0 && (rc = set_smem(h, k_solve<MODEL, GG, true>, box_smem))) return rc;       \
     k_solve<MODEL, GG, true><<<(unsigned)blocks, block, box_smem, st>>>(k, *sp, a);            \
   } while (0)
 #define MPCB_LAUNCH_T_G(MODEL)                                                                 \
@@ -458,34 +471,62 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     int64_t round = 0;
     const int64_t round_cap = 4000000;
     int chunk = 48;
+    for (cudaEvent_t& ev : h->rs_ev) if (!ev) CK(cudaEventCreate(&ev));
+    if (h->debug_timers >= 2) {
+      unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      CK(cudaMemcpyToSymbolAsync(g_dbg_calls, z, sizeof(z), 0, cudaMemcpyHostToDevice, st));
+    }
+    std::FILE* log = h->round_log ? std::fopen(h->round_log, "w") : nullptr;
+    h->last_eval_ms = 0.0; h->last_trans_ms = 0.0;
     for (;;) {
       for (int i = 0; i < chunk; ++i, ++round) {
         a.round = (int)round;
         e.counters = h->rs_counters + 4 * (round & 1);
+        CK(cudaEventRecord(h->rs_ev[3 * i], st));
         if (k.model_id == MPCB_MODEL_PACEJKA6) {
           MPCB_LAUNCH_T_G(MPCB_MODEL_PACEJKA6)
-          k_eval_requests<MPCB_MODEL_PACEJKA6><<<(unsigned)eblocks, 128, road_smem, st>>>(k, e);
+          CK(cudaEventRecord(h->rs_ev[3 * i + 1], st));
+          k_eval_requests<MPCB_MODEL_PACEJKA6><<<(unsigned)eblocks, 256, road_smem, st>>>(k, e);
         } else {
           MPCB_LAUNCH_T_G(MPCB_MODEL_KINEMATIC4)
-          k_eval_requests<MPCB_MODEL_KINEMATIC4><<<(unsigned)eblocks, 128, road_smem, st>>>(k, e);
+          CK(cudaEventRecord(h->rs_ev[3 * i + 1], st));
+          k_eval_requests<MPCB_MODEL_KINEMATIC4><<<(unsigned)eblocks, 256, road_smem, st>>>(k, e);
         }
+        CK(cudaEventRecord(h->rs_ev[3 * i + 2], st));
+        if (log || i == chunk - 1)
+          CK(cudaMemcpyAsync(h->rs_counters_host + 4 * i, h->rs_counters + 4 * (round & 1), 4 * sizeof(unsigned),
+                             cudaMemcpyDeviceToHost, st));
       }
       h->launches += 2 * chunk;
       CK(cudaGetLastError());
-      CK(cudaMemcpyAsync(h->rs_counters_host, h->rs_counters + 4 * ((round - 1) & 1), 4 * sizeof(unsigned),
-                         cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
-      if (h->rs_counters_host[0] == 0 && h->rs_counters_host[1] == 0) break;
+      for (int i = 0; i < chunk; ++i) {
+        float t1 = 0.f, t2 = 0.f;
+        CK(cudaEventElapsedTime(&t1, h->rs_ev[3 * i], h->rs_ev[3 * i + 1]));
+        CK(cudaEventElapsedTime(&t2, h->rs_ev[3 * i + 1], h->rs_ev[3 * i + 2]));
+        h->last_trans_ms += t1; h->last_eval_ms += t2;
+        if (log) std::fprintf(log, "%lld %u %u %.4f %.4f\n", (long long)(round - chunk + i), h->rs_counters_host[4 * i],
+                              h->rs_counters_host[4 * i + 1], t1, t2);
+      }
+      const unsigned* last = h->rs_counters_host + 4 * (chunk - 1);
+      if (last[0] == 0 && last[1] == 0) break;
       if (round > round_cap) return fail(h, MPCB_E_CUDA, "mpcb_solve: round cap exceeded");
       chunk = 24;
     }
 #undef MPCB_LAUNCH_T_G
 #undef MPCB_LAUNCH_T
+    if (log) std::fclose(log);
+    if (h->debug_timers >= 2) {
+      unsigned long long c[8];
+      if (cudaMemcpyFromSymbol(c, g_dbg_calls, sizeof(c)) == cudaSuccess)
+        std::fprintf(stderr, "[mpcb debug] model calls by lane: fast %llu wide %llu nan %llu slow %llu; warp calls %llu, "
+                     "with a wide lane %llu, with a slow lane %llu\n", c[0], c[2], c[3], c[4], c[5], c[6], c[7]);
+    }
     h->last_rounds = round;
     return leave(h, st);
   }
   if (h->debug_timers) {
-    unsigned long long z[2] = {0, 0};
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     CK(cudaMemcpyToSymbolAsync(g_dbg_calls, z, sizeof(z), 0, cudaMemcpyHostToDevice, st));
     if ((rc = grow(h, &h->dbg, &h->dbg_cap, (size_t)(ns / 32) * 4 * sizeof(long long), st))) return rc;
     CK(cudaMemsetAsync(h->dbg, 0, (size_t)(ns / 32) * 4 * sizeof(long long), st));

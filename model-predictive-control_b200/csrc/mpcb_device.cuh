@@ -47,7 +47,7 @@ MPCB_DEV void load_vehicle(VehP* v, const double* __restrict__ p, const KDesc& d
 // Problem description and vehicle constants of the running kernel, at file scope in shared memory so the
 // non-inlined evaluation function (mpcb_fwd.cuh) reads them with LDS instead of through generic pointers.
 // MPCB_DEBUG_TIMERS diagnostics: model calls that took the fast / general path (lane granularity)
-__device__ unsigned long long g_dbg_calls[2];
+__device__ unsigned long long g_dbg_calls[8];  // fast, general (= wide + nan + slow) lanes; wide, nan, slow lanes; warp calls, with wide, with slow
 static __shared__ VehP s_veh;
 static __shared__ KDesc s_desc;
 // Called by every thread of a kernel before it evaluates anything (ends with a block barrier).

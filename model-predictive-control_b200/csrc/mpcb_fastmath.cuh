@@ -158,6 +158,30 @@ MPCB_FM_FN void fm_atan_nr_x2(double x1, double x2, double* y1, double* y2) {
   *y2 = fma(x2 * z2, p2, x2);
 }
 
+// atan of two arguments of any magnitude, branch-free (selects only): |x| > 1 goes through 1/|x|, and each
+// argument takes the short polynomial when |x| <= 0.5 (or when the caller forces it: `force_small` lanes get
+// exactly fm_atan_nr_x2<true>'s bits) and the full one otherwise — the same arithmetic, argument by argument,
+// as fm_atan below.  NaN -> NaN, +-Inf -> +-pi/2.
+MPCB_FM_FN void fm_atan_any_x2(double x1, double x2, bool force_small, double* y1, double* y2) {
+  const double ax1 = fabs(x1), ax2 = fabs(x2);
+  const bool big1 = !force_small && ax1 > 1.0, big2 = !force_small && ax2 > 1.0;
+  const bool sm1 = force_small || ax1 <= 0.5, sm2 = force_small || ax2 <= 0.5;
+  const double rc1 = fm_rcp(fmin(fmax(ax1, 1.0), 0x1p1000)), rc2 = fm_rcp(fmin(fmax(ax2, 1.0), 0x1p1000));
+  // forced lanes keep the signed argument: fma(x z, p, x) exactly as fm_atan_nr_x2 (the sign of a zero result included)
+  const double t1 = force_small ? x1 : (big1 ? (ax1 < 0x1p1000 ? rc1 : 0.0) : ax1);
+  const double t2 = force_small ? x2 : (big2 ? (ax2 < 0x1p1000 ? rc2 : 0.0) : ax2);
+  const double z1 = t1 * t1, z2 = t2 * t2;
+  double ps1, ps2, pf1, pf2;
+  fm_poly_atan_small_x2(z1, z2, &ps1, &ps2);
+  fm_poly_atan_full_x2(z1, z2, &pf1, &pf2);
+  double r1 = fma(t1 * z1, sm1 ? ps1 : pf1, t1), r2 = fma(t2 * z2, sm2 ? ps2 : pf2, t2);
+  const double c1 = (MPCB_FM_PIO2_1 - r1) + MPCB_FM_PIO2_2, c2 = (MPCB_FM_PIO2_1 - r2) + MPCB_FM_PIO2_2;
+  r1 = big1 ? c1 : r1;
+  r2 = big2 ? c2 : r2;
+  *y1 = force_small ? r1 : copysign(r1, x1);
+  *y2 = force_small ? r2 : copysign(r2, x2);
+}
+
 // ---- general versions (any argument; branchy: slow path of the model call, utility kernels) -------
 MPCB_FM_FN void fm_sincos(double x, double* s, double* c) {
   if (!(fabs(x) < MPCB_FM_TRIG_MAX)) {  // huge / NaN / Inf: library path

@@ -97,6 +97,36 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     else fm_sin_nr_x2(v.cf * uf, v.cr * ur, &stf, &str_);
     finish<GRAD>(q, su, v, s, c, a_f, a_r, zf, zr, stf, ctf, str_, ctr, 1.0, kp, kq, L);
   }
+  // Wide path: any slip angle and either sign of vx, still one branch-free block (full-range atan by
+  // selects, the +-pi of atan2's left half-plane by a select).  Preconditions: vx normal and non-zero,
+  // a_f, a_r finite, |phi| < 2^17, VehP.trig_ok.  A lane that also meets call_fast's preconditions
+  // (`is_fast`) gets call_fast's result bit for bit, so a warp in which SOME lane needs the wide path runs
+  // all its lanes through it once instead of running both paths back to back — line-search candidates
+  // that brake to a standstill or spin out made that the common case of the solver's evaluation rounds
+  // (profiles/r01_round_mode.md).
+  template <bool GRAD>
+  static MPCB_DEV void call_wide(const double* q, const StageU& su, const VehP& v, double a_f, double a_r, bool is_fast,
+                                 double* kp, double* kq, Lin& L) {
+    double s, c;
+    fm_sincos_nr(q[0], &s, &c);
+    const double vx = q[1];
+    const double r = fm_rcp(vx);
+    double thf, ar;
+    fm_atan_any_x2(a_f * r, a_r * r, is_fast, &thf, &ar);
+    const bool rev = vx < 0.0;  // atan2(a, vx) = atan(a / vx) + copysign(pi, a) in the left half-plane
+    const double pf = copysign(2.0 * MPCB_FM_PIO2_1, a_f), pr = copysign(2.0 * MPCB_FM_PIO2_1, a_r);
+    const double pfl = copysign(2.0 * MPCB_FM_PIO2_2, a_f), prl = copysign(2.0 * MPCB_FM_PIO2_2, a_r);
+    thf = rev ? (thf + pf) + pfl : thf;
+    ar = rev ? (ar + pr) + prl : ar;
+    const double af = su.dl - thf;
+    const double zf = v.bf * af, zr = v.br * ar;
+    double uf, ur;
+    fm_atan_any_x2(zf, zr, is_fast, &uf, &ur);
+    double stf, ctf = 0.0, str_, ctr = 0.0;
+    if (GRAD) fm_sincos_nr_x2(v.cf * uf, v.cr * ur, &stf, &ctf, &str_, &ctr);
+    else fm_sin_nr_x2(v.cf * uf, v.cr * ur, &stf, &str_);
+    finish<GRAD>(q, su, v, s, c, a_f, a_r, zf, zr, stf, ctf, str_, ctr, rev ? -1.0 : 1.0, kp, kq, L);
+  }
   // General path: reversing / standstill / large slip / non-finite states.
   template <bool GRAD>
   static MPCB_DEV void call_slow(const double* q, const StageU& su, const VehP& v, double a_f, double a_r,
@@ -129,8 +159,45 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     const bool ok = vx > 0x1p-960 && vx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX;
     const bool fast = ok && su.z2_mode == 2 && am <= 0.5 * vx;
     if (s_desc.debug >= 2) atomicAdd(&g_dbg_calls[fast ? 0 : 1], 1ull);  // MPCB_DEBUG_TIMERS=2
-    if (fast) call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
-    else call_slow<GRAD>(q, su, v, a_f, a_r, kp, kq, L);  // slip beyond atan(0.5) = 26.6 deg, reversing, ...
+    const double avx = fabs(vx);
+    const bool wide = !fast && avx > 0x1p-960 && avx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX && v.trig_ok &&
+                      fabs(a_f) < 0x1p1000 && fabs(a_r) < 0x1p1000;
+    // The vote only picks which of two bit-identical routes the fast lanes take, so any set of voters is fine.
+    const unsigned act = __activemask();
+    const bool any_wide = __ballot_sync(act, wide) != 0u;
+    if (s_desc.debug >= 2) {
+      const bool is_nan_d = !(q[0] == q[0] && vx == vx && q[2] == q[2] && q[3] == q[3]);
+      const bool slow_d = !fast && !wide && !is_nan_d;
+      if (!fast) atomicAdd(&g_dbg_calls[wide ? 2 : (is_nan_d ? 3 : 4)], 1ull);
+      const unsigned sl = __ballot_sync(act, slow_d);
+      if ((act & (0u - act)) == (1u << (threadIdx.x & 31))) {
+        atomicAdd(&g_dbg_calls[5], 1ull);
+        if (any_wide) atomicAdd(&g_dbg_calls[6], 1ull);
+        if (sl) atomicAdd(&g_dbg_calls[7], 1ull);
+      }
+    }
+    if (!any_wide) {
+      if (fast) call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
+    } else {
+      if (fast || wide) call_wide<GRAD>(q, su, v, a_f, a_r, fast, kp, kq, L);
+    }
+    if (!fast && !wide) {
+      // A NaN velocity/heading stays NaN through every later RK4 element and makes the cost NaN whatever the
+      // other components are, so such a lane (a line-search candidate that blew up: x + q is not box-feasible
+      // and the drive force feeds back on vx exponentially) is given NaN outputs at once instead of dragging
+      // its warp through the library sin/cos/atan2 of the general path for the rest of the horizon.
+      const bool is_nan = !(q[0] == q[0] && vx == vx && q[2] == q[2] && q[3] == q[3]);
+      if (is_nan) {
+        const double nn = q[0] + vx + q[2] + q[3];
+        kp[0] = nn; kp[1] = nn; kq[0] = nn; kq[1] = nn; kq[2] = nn; kq[3] = nn;
+        if (GRAD) {
+          L.s = nn; L.c = nn; L.f0 = nn; L.f1 = nn; L.a11 = nn; L.a12 = nn; L.a13 = nn; L.a21 = nn; L.a22 = nn; L.a23 = nn;
+          L.a31 = nn; L.a32 = nn; L.a33 = nn; L.bd = nn; L.bl1 = nn; L.bl2 = nn; L.bl3 = nn;
+        }
+      } else {
+        call_slow<GRAD>(q, su, v, a_f, a_r, kp, kq, L);  // standstill, infinite or huge states
+      }
+    }
   }
   // tangent of one direction J at the same stage point: tq = (phi', vx', vy', w')
   template <int J>

@@ -110,6 +110,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   else stage_problem(d, a.p);
   const double* lbv = sbox;
   const double* ubv = sbox + n;
+  // two-loop recursion scalars (rho_i, alpha_i) of this CTA's tiles: [tile in CTA][2 * mem]
+  double* const s_ra = sbox + 2 * n + (threadIdx.x / G) * 2 * mem;
 
   const int64_t ns = a.ns, nt = a.nt;
   const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -211,6 +213,19 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   auto lbfgs_apply = [&]() {
     const int cnt = lb_full ? mem : lb_idx;
     double H0 = -1.0;
+    // The history of a large batch lives in DRAM (13 KB per tile): ask for all of it at once, so the
+    // dependent chain below (every step needs the q of the previous one) waits on L2 hits instead.
+    for (int kk = 0; kk < cnt; ++kk) {
+      int i = lb_idx - 1 - kk;
+      if (i < 0) i += mem;
+      for (int j = 0; j < ne; j += (G >= 16 ? 1 : 16 / G)) {  // one request per 128-byte line of the tile's row
+        int e = l + G * j;
+        if (e < n) {
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&tv(T.LS + i * T.np, e)));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&tv(T.LY + i * T.np, e)));
+        }
+      }
+    }
     for (int kk = 0; kk < cnt; ++kk) {
       int i = lb_idx - 1 - kk;
       if (i < 0) i += mem;
@@ -223,12 +238,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         }
       }
       sy = tsum(sy); yy = tsum(yy); sq = tsum(sq);
-      if (!(sy > 0.0)) { TR(T.RH, i) = nan(""); continue; }
+      if (!(sy > 0.0)) { s_ra[i] = nan(""); continue; }
       double rho = 1.0 / sy;
-      TR(T.RH, i) = rho;
+      s_ra[i] = rho;
       if (H0 < 0.0) H0 = sy / yy;
       double al = rho * sq;
-      TR(T.AL, i) = al;
+      s_ra[mem + i] = al;
       for (int j = 0; j < ne; ++j) {
         int e = l + G * j;
         if (e < n && mbit(e)) tv(T.Q, e) -= al * tv(T.LY + i * T.np, e);
@@ -242,7 +257,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     for (int kk = cnt - 1; kk >= 0; --kk) {
       int i = lb_idx - 1 - kk;
       if (i < 0) i += mem;
-      double rho = TR(T.RH, i);
+      double rho = s_ra[i];
       if (isnan(rho)) continue;
       double yq = 0.0;
       for (int j = 0; j < ne; ++j) {
@@ -250,7 +265,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         if (e < n && mbit(e)) yq += tv(T.LY + i * T.np, e) * tv(T.Q, e);
       }
       yq = tsum(yq);
-      double coef = TR(T.AL, i) - rho * yq;
+      double coef = s_ra[mem + i] - rho * yq;
       for (int j = 0; j < ne; ++j) {
         int e = l + G * j;
         if (e < n && mbit(e)) tv(T.Q, e) += coef * tv(T.LS + i * T.np, e);
@@ -847,8 +862,14 @@ struct EvalArgs {
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
 };
 
+// Launch shape: ONE CTA of 256 lanes per SM, so a CTA's warps w and w + 4 share an SM sub-partition and
+// the first chunk of every warp is assigned statically, sub-partition by sub-partition across the whole GPU
+// (chunk c -> SM c % gridDim, warp (c / gridDim) % 8): up to 4 x SMs chunks run one per sub-partition, the
+// next 4 x SMs double up, and only beyond that do warps pull further chunks from the work counter.  (With
+// two 128-lane CTAs per SM and a purely dynamic queue ncu showed sub-partitions holding 4 busy warps next
+// to idle ones: 2.2 M cycles elapsed for 0.95 M cycles of average SM activity, profiles/r01_round_mode.md.)
 template <int MODEL>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256, 1)
 k_eval_requests(KDesc d, EvalArgs e) {
   constexpr int NX = Fm<MODEL>::NX;
   extern __shared__ double smem[];
@@ -861,10 +882,17 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const Vec scr{e.escr + eslot, e.ens};
   const unsigned ng = e.counters[0], nv = e.counters[1];
   const unsigned cg = (ng + 31u) >> 5, cv = (nv + 31u) >> 5;
+  const unsigned n_warps = gridDim.x * (blockDim.x >> 5);
+  bool first = true;
   for (;;) {
     unsigned c = 0;
-    if (lane == 0) c = atomicAdd(&e.counters[2], 1u);
-    c = __shfl_sync(0xffffffffu, c, 0);
+    if (first) {
+      c = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+      first = false;
+    } else {
+      if (lane == 0) c = n_warps + atomicAdd(&e.counters[2], 1u);
+      c = __shfl_sync(0xffffffffu, c, 0);
+    }
     if (c >= cg + cv) break;
     const bool grad = c < cg;
     const unsigned idx = ((grad ? c : c - cg) << 5) + (unsigned)lane;

@@ -94,6 +94,13 @@ class BatchedMpc:
     def launch_count(self):
         return int(self._lib.mpcb_launch_count(self._h))
 
+    def last_solve_profile(self):
+        """dict(mode, tile, rounds, eval_ms, trans_ms, eval_launches) of the last solve (CUDA events inside the library)."""
+        out = (C.c_double * 6)()
+        self._lib.mpcb_last_solve_profile(self._h, out)
+        return dict(mode="rounds" if out[0] else "persistent", tile=int(out[1]), rounds=int(out[2]), eval_ms=out[3],
+                    trans_ms=out[4], eval_launches=int(out[5]))
+
     def default_solver_params(self):
         return _ffi.default_solver_params(self.N)
 

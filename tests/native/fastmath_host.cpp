@@ -25,4 +25,7 @@ void fmh_atan_x2(const double* x, double* y, long n, int small) {
     else mpcb::fm_atan_nr_x2<false>(x[i], x[i + 1], &y[i], &y[i + 1]);
   }
 }
+void fmh_atan_any_x2(const double* x, double* y, long n, int force_small) {
+  for (long i = 0; i + 1 < n; i += 2) mpcb::fm_atan_any_x2(x[i], x[i + 1], force_small != 0, &y[i], &y[i + 1]);
+}
 }

@@ -28,6 +28,7 @@ def fm():
     lib.fmh_sincos_x2.argtypes = [dp, dp, dp, C.c_long]
     lib.fmh_sin_x2.argtypes = [dp, dp, C.c_long]
     lib.fmh_atan_x2.argtypes = [dp, dp, C.c_long, C.c_int]
+    lib.fmh_atan_any_x2.argtypes = [dp, dp, C.c_long, C.c_int]
     return lib
 
 
@@ -94,3 +95,31 @@ def test_paired_branch_free_cores(fm):
         assert _ulps(y[ok], ref[ok]).max() <= 2.0
         nz = a != 0  # the branch-free form returns +0 for -0 (irrelevant to the model)
         assert np.all(np.signbit(y[nz]) == np.signbit(a[nz]))
+
+
+def test_wide_path_atan_is_the_general_atan_and_the_fast_atan(fm):
+    """fm_atan_any_x2 (the model call's wide path): bit-identical to the branchy fm_atan for every argument, and —
+    with force_small — bit-identical to the fast path's fm_atan_nr_x2<true>, which is what lets a warp route its
+    fast lanes through the wide path without changing their results."""
+    rng = np.random.default_rng(4)
+    x = np.concatenate([rng.uniform(-0.5, 0.5, 100000), rng.uniform(-1, 1, 100000), rng.uniform(-50, 50, 100000),
+                        10.0 ** rng.uniform(-300, 300, 100000) * rng.choice([-1, 1], 100000),
+                        np.array([0.0, -0.0, 0.5, -0.5, 1.0, -1.0, 1e300, -1e308, np.inf, -np.inf, 5e-324, 1.0000000000000002])])
+    if x.size % 2:
+        x = x[:-1]
+    y_any, y_gen = np.empty_like(x), np.empty_like(x)
+    fm.fmh_atan_any_x2(_ptr(x), _ptr(y_any), x.size, 0)
+    fm.fmh_atan(_ptr(x), _ptr(y_gen), x.size)
+    assert np.array_equal(y_any.view(np.uint64), y_gen.view(np.uint64))
+    ref = np.arctan(x)
+    ok = (ref != 0) & (np.abs(x) > 1e-300)
+    assert _ulps(y_any[ok], ref[ok]).max() <= 2.0
+    n = np.array([np.nan, 0.3])
+    out = np.empty(2)
+    fm.fmh_atan_any_x2(_ptr(n), _ptr(out), 2, 0)
+    assert np.isnan(out[0]) and abs(out[1] - np.arctan(0.3)) < 1e-16
+    a = np.concatenate([rng.uniform(-0.5, 0.5, 200000), np.array([0.0, -0.0, 0.5, -0.5, 1e-200, -1e-9])])
+    y_forced, y_fast = np.empty_like(a), np.empty_like(a)
+    fm.fmh_atan_any_x2(_ptr(a), _ptr(y_forced), a.size, 1)
+    fm.fmh_atan_x2(_ptr(a), _ptr(y_fast), a.size, 1)
+    assert np.array_equal(y_forced.view(np.uint64), y_fast.view(np.uint64))

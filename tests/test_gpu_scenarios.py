@@ -1,0 +1,113 @@
+"""GPU tests of the batched scenario drivers (§8f-1) through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mp():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    import mpcb200
+    return mpcb200
+
+
+def test_closed_loop_tracks_oracle_loop(mp, orc):
+    """Config 1 (main.py:121-152) for a small batch: the device loop against the same loop driven by the oracle
+    (oracle solve + oracle RK4 plant), warm start unshifted as in controller.py:57.  States agree to the solve
+    tolerance; both keep every tick converged."""
+    from mpcb200 import scenarios as sc, workloads as wl
+    N, B, S, ticks = 12, 16, 100, 6
+    w = wl.tracking_batch(B, N, S, seed=21)
+    prob = mp.BatchedMpc(N=N, S=S, road_mode=mp.ROAD_TABLE, n_roads=2)
+    r = sc.closed_loop(prob, w["x0"], w["road"], ticks, road_idx=w["road_idx"], record_U=True)
+    assert (r["status"].cpu().numpy() == 1).all() and int(r["failures"].sum()) == 0
+    d = orc.default_desc(0, N, S)
+    d.road_mode, d.n_roads = 1, 2
+    sp = orc.default_solver_params(N)
+    x, U = w["x0"].copy(), w["U0"].copy()
+    xs = [x.copy()]
+    for t in range(ticks):
+        o = orc.solve(d, sp, x, w["road"], U, road_idx=w["road_idx"])
+        assert (o["status"] == 1).all()
+        U = o["U"]
+        x = np.stack([orc.rk4_stage(d, x[i], U[i, :2]) for i in range(B)])
+        xs.append(x.copy())
+    xs = np.stack(xs)
+    err = np.abs(r["states"].cpu().numpy() - xs).max(axis=(0, 2))
+    print(f"closed loop {ticks} ticks: max state deviation median {np.median(err):.2e} max {err.max():.2e}")
+    assert np.median(err) < 1e-5 and err.max() < 1e-3
+    # the plant step is the stage map of the rollout: first predicted state == next measured state
+    st, _, _ = prob.rollout(r["states"][0], r["U_ticks"][0], w["road"], road_idx=w["road_idx"])
+    np.testing.assert_allclose(st[:, 0].cpu().numpy(), r["states"][1].cpu().numpy(), rtol=1e-12, atol=1e-14)
+
+
+def test_closed_loop_shifted_warm_start_needs_fewer_iterations(mp):
+    from mpcb200 import scenarios as sc, workloads as wl
+    N, B, S, ticks = 20, 64, 100, 5
+    w = wl.tracking_batch(B, N, S, seed=22)
+    prob = mp.BatchedMpc(N=N, S=S, road_mode=mp.ROAD_TABLE, n_roads=2)
+    a = sc.closed_loop(prob, w["x0"], w["road"], ticks, road_idx=w["road_idx"], shift=False)
+    b = sc.closed_loop(prob, w["x0"], w["road"], ticks, road_idx=w["road_idx"], shift=True)
+    ia, ib = a["inner"].double().mean(dim=1).cpu().numpy(), b["inner"].double().mean(dim=1).cpu().numpy()
+    print(f"mean inner iterations per tick: unshifted {ia.round(1)}, shifted {ib.round(1)}")
+    assert (a["status"].cpu().numpy() == 1).all() and (b["status"].cpu().numpy() == 1).all()
+    assert ia[0] == ib[0]                   # tick 0 is the same cold solve
+    assert ia[1:].mean() < 0.5 * ia[0]      # warm starts pay off (controller.py:57)
+    assert ib[1:].mean() <= ia[1:].mean() * 1.05
+
+
+def test_event_triggered_resolve(mp, orc):
+    """Config 3 at test size: Kinematic-4, N = 40, Bezier lane-change roads, 2 moving obstacles, lane potentials.
+    The warm re-solve from a perturbed state needs far fewer iterations than the cold solve, and both agree
+    with the oracle run on the same inputs."""
+    from mpcb200 import scenarios as sc, workloads as wl
+    B, N, S, n_obs = 48, 40, 100, 2
+    lc = wl.lane_change_batch(B, N, S, seed=3, n_obs=n_obs)
+    flags = mp.FLAG_LANE | mp.FLAG_OBST
+    prob = mp.BatchedMpc(N=N, S=S, model_id=1, road_mode=mp.ROAD_BEZIER, flags=flags, n_obs=n_obs, v_ref=20.0)
+    U_cold, st_c, x1, U_warm, st_w = sc.event_triggered_resolve(prob, lc["x0"], lc["ctrl"], lc["U0"], obs=lc["obs"],
+                                                               sigma=0.02, seed=5)
+    sc_, sw_ = st_c.status.cpu().numpy(), st_w.status.cpu().numpy()
+    ic, iw = st_c.inner_iterations.cpu().numpy(), st_w.inner_iterations.cpu().numpy()
+    print(f"cold: converged {np.mean(sc_ == 1):.3f}, inner mean {ic.mean():.1f}; warm: converged {np.mean(sw_ == 1):.3f}, "
+          f"inner mean {iw.mean():.1f}")
+    assert np.mean(sc_ == 1) > 0.9 and np.mean(sw_ == 1) > 0.9
+    assert iw.mean() < 0.6 * ic.mean()
+    d = orc.default_desc(1, N, S)
+    d.road_mode, d.n_roads, d.flags, d.n_obs, d.v_ref = 3, 1, flags, n_obs, 20.0
+    o = orc.solve(d, orc.default_solver_params(N), x1.cpu().numpy(), lc["ctrl"], U_cold.cpu().numpy(), obs=lc["obs"])
+    ok = (sw_ == 1) & (o["status"] == 1)
+    gap = np.abs(st_w.psi.cpu().numpy() - o["psi"])[ok] / np.maximum(np.abs(o["psi"][ok]), 1e-12)
+    err = np.abs(U_warm.cpu().numpy() - o["U"]).max(axis=1)[ok]
+    print(f"warm re-solve vs oracle: both converged {ok.mean():.3f}, |dU| median {np.median(err):.2e}, psi gap median {np.median(gap):.1e}")
+    assert ok.mean() > 0.9
+    assert np.median(err) < 3e-4 and np.median(gap) < 1e-6
+
+
+def test_best_response_rounds_single_rank(mp):
+    """Config 4 on one rank: vehicle pairs plan against each other's announced trajectories; the exchange is the
+    identity at world size 1.  Every solve converges, the gathered trajectories have the [2P, N, 4] layout, the
+    obstacle records are the opponents' states, and a second call reproduces the first bit for bit."""
+    import torch
+    from mpcb200 import scenarios as sc, workloads as wl
+    P, N, S = 24, 20, 100
+    nv = 2 * P
+    lc = wl.lane_change_batch(nv, N, S, seed=9, n_obs=1)
+    x0 = lc["x0"].copy()
+    x0[P:, 0] += 30.0          # vehicle B of every pair starts ahead in the target lane
+    x0[P:, 1] += 3.75
+    x0[P:, 3] -= 6.0
+    prob = mp.BatchedMpc(N=N, S=S, model_id=1, road_mode=mp.ROAD_BEZIER, flags=mp.FLAG_LANE | mp.FLAG_OBST, n_obs=1,
+                         v_ref=20.0)
+    r1 = sc.best_response_rounds(prob, x0, lc["ctrl"], nv, rounds=3)
+    r2 = sc.best_response_rounds(prob, x0, lc["ctrl"], nv, rounds=3)
+    assert tuple(r1["traj"].shape) == (nv, N, 4)
+    assert (r1["status"].cpu().numpy() == 1).mean() > 0.9
+    assert torch.equal(r1["U"], r2["U"]) and torch.equal(r1["traj"], r2["traj"])
+    opp = sc.opponent_index(nv).numpy()
+    np.testing.assert_array_equal(r1["obs"][:, 0, :4].cpu().numpy(), x0[opp])
+    print(f"best response: trajectory change per round {r1['delta']}")
+    assert r1["delta"][2] <= r1["delta"][1] * 1.5 + 1e-9

@@ -33,6 +33,8 @@ def main():
         import numpy as np
         buf = (C.c_longlong * (4 * 4096))()
         nw = mpcb200._ffi.lib().mpcb_debug_timers(prob._h, buf, 4096)
+        if nw == 0:
+            return
         t = np.frombuffer(buf, dtype=np.int64)[:4 * nw].reshape(nw, 4).astype(float)
         tot = t[:, 0] + t[:, 1]
         i = int(np.argmax(tot))
