@@ -386,13 +386,18 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   //    enqueues rounds ahead of the GPU and reads the request counters every few dozen rounds to stop.
   // Tile width: spare lanes are spent on speculative line-search candidates (mpcb_solve.cuh).
   const int block = 64;
-  const int mode = h->mode_override >= 0 ? h->mode_override : 1;
+  // small batches: one asynchronous persistent launch; from a few thousand instances on the rounds win
+  // (profiles/r01_round_mode.md: 395 vs 413 ms at B = 4096, 2.8 vs 6.9 s at B = 65536)
+  const int mode = h->mode_override >= 0 ? h->mode_override : (B >= 2048 ? 1 : 0);
   const int64_t lane_cap = (int64_t)h->num_sms * h->warps_per_sm * 32;
   int G = 1;
   if (mode == 1) {
     // rounds: idle lanes cost nothing in the evaluation launch; speculation pays until the evaluation launch
     // is throughput-bound (about 4 requests per evaluating lane in flight)
-    G = B <= 8192 ? 8 : (B <= 16384 ? 4 : (B <= 32768 ? 2 : 1));
+    // measured (profiles/r01_round_mode.md): G = 8 wins at every batch size up to 65536 (fewest rounds; idle lanes are
+    // free); narrower tiles only to keep the per-lane workspace of very large batches within ~8 GB
+    G = 8;
+    while (G > 1 && (double)B * G * (8.0 * k.n + (k.bounded ? k.N * k.nx : 0)) * 8.0 > 8e9) G >>= 1;
   } else {
     for (int g : {8, 4, 2}) if (B * g <= (int64_t)h->num_sms * 8 * 32) { G = g; break; }
   }
@@ -425,7 +430,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   h->last_mode = mode;
   if (mode == 1) {
     // evaluation launch: one CTA of 256 lanes (255 registers each) per SM, never more lanes than requests can exist
-    int64_t eblocks = (ns + 255) / 256;
+    int64_t eblocks = (ns + 31) / 32;   // one warp per SM sub-partition before any doubling up
     if (eblocks > (int64_t)h->num_sms) eblocks = (int64_t)h->num_sms;
     const int64_t ens = eblocks * 256;
     if ((rc = grow(h, &h->rs_d, &h->rs_d_cap, (size_t)MPCB_SD_ROWS * ns * sizeof(double), st))) return rc;
