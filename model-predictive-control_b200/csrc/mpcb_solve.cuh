@@ -126,7 +126,9 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   // row `row` of tile lane `ll` (lane-interleaved)
   auto WL = [&](int row, int ll) { return Vec{a.ws + (int64_t)row * ns + (slot - l + ll), ns}; };
   // element i of the tile-vector at offset `off` (off is a multiple of G)
-  auto tv = [&](int off, int i) -> double& { return a.wst[((int64_t)((off + i) / G) * nt + tile) * G + (i % G)]; };
+  double* const wtile = a.wst + tile * G;
+  const int64_t ntG = nt * G;
+  auto tv = [&](int off, int i) -> double& { return wtile[(int64_t)((off + i) / G) * ntG + ((off + i) % G)]; };
   double* const trow = a.wst + (int64_t)T.vec_total * nt;  // plain per-tile rows
   auto TR = [&](int off, int i) -> double& { return trow[(int64_t)(off - T.vec_total + i) * nt + tile]; };
   auto tsync = [&]() { __syncwarp(tmask); };
@@ -194,22 +196,41 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
 
   // x̂ = Π_C(x − γ g), p = x̂ − x (stored into XH, P); returns gᵀp and pᵀp
   auto prox = [&](const Vec& X, const Vec& Gv, double gamma, const Vec& XH, const Vec& P, double& gtp, double& ptp) {
+    // Loads of 8 elements are issued together, then the arithmetic and the stores: the compiler cannot move a
+    // load above an earlier store through another Vec, which serialised n DRAM round trips per call (ncu:
+    // 12 % of the transition launch's samples on this loop's first use of a loaded value).
     double s1 = 0.0, s2 = 0.0;
-    for (int i = 0; i < n; ++i) {
-      double xi = X(i), gi = Gv(i);
-      double t = fma(-gamma, gi, xi);
-      t = t < lbv[i] ? lbv[i] : (t > ubv[i] ? ubv[i] : t);
-      double pi = t - xi;
-      XH.set(i, t);
-      P.set(i, pi);
-      s1 += gi * pi;
-      s2 += pi * pi;
+    for (int i0 = 0; i0 < n; i0 += 8) {
+      double xv[8], gv[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const bool in = i0 + k < n;
+        xv[k] = in ? X(i0 + k) : 0.0;
+        gv[k] = in ? Gv(i0 + k) : 0.0;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int i = i0 + k;
+        if (i < n) {
+          double t = fma(-gamma, gv[k], xv[k]);
+          t = t < lbv[i] ? lbv[i] : (t > ubv[i] ? ubv[i] : t);
+          double pi = t - xv[k];
+          XH.set(i, t);
+          P.set(i, pi);
+          s1 += gv[k] * pi;
+          s2 += pi * pi;
+        }
+      }
     }
     gtp = s1;
     ptp = s2;
   };
 
-  // q <- H q on the inactive set (masked two-loop recursion, Appendix A 3c), split over the tile.
+  // q <- H q on the inactive set (masked two-loop recursion, Appendix A 3c), split over the tile: lane l owns the
+  // elements e = l + G j.  With at most NQ of them per lane (G = 8: n <= 80) q stays in registers for the whole
+  // recursion — the global read-modify-write of q per history pair (and the store/load ordering it imposed)
+  // was a third of the transition launch's samples — and the dot products run in the same order as before.
+  constexpr int NQ = 10;
   auto lbfgs_apply = [&]() {
     const int cnt = lb_full ? mem : lb_idx;
     double H0 = -1.0;
@@ -225,6 +246,69 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           asm volatile("prefetch.global.L2 [%0];" ::"l"(&tv(T.LY + i * T.np, e)));
         }
       }
+    }
+    if (ROUND && ne <= NQ) {  // (the persistent kernel has no registers to spare: it spilled with this path)
+      double q[NQ];
+      bool own[NQ];
+#pragma unroll
+      for (int j = 0; j < NQ; ++j) {
+        const int e = l + G * j;
+        own[j] = j < ne && e < n && mbit(e);
+        q[j] = own[j] ? tv(T.Q, e) : 0.0;
+      }
+      for (int kk = 0; kk < cnt; ++kk) {
+        int i = lb_idx - 1 - kk;
+        if (i < 0) i += mem;
+        double sv[NQ], yv[NQ];
+#pragma unroll
+        for (int j = 0; j < NQ; ++j) {
+          sv[j] = own[j] ? tv(T.LS + i * T.np, l + G * j) : 0.0;
+          yv[j] = own[j] ? tv(T.LY + i * T.np, l + G * j) : 0.0;
+        }
+        double sy = 0.0, yy = 0.0, sq = 0.0;
+#pragma unroll
+        for (int j = 0; j < NQ; ++j)
+          if (own[j]) { sy += sv[j] * yv[j]; yy += yv[j] * yv[j]; sq += sv[j] * q[j]; }
+        sy = tsum(sy); yy = tsum(yy); sq = tsum(sq);
+        if (!(sy > 0.0)) { s_ra[i] = nan(""); continue; }
+        double rho = 1.0 / sy;
+        s_ra[i] = rho;
+        if (H0 < 0.0) H0 = sy / yy;
+        double al = rho * sq;
+        s_ra[mem + i] = al;
+#pragma unroll
+        for (int j = 0; j < NQ; ++j)
+          if (own[j]) q[j] -= al * yv[j];
+      }
+      if (!(H0 >= 0.0)) H0 = gam;
+#pragma unroll
+      for (int j = 0; j < NQ; ++j)
+        if (own[j]) q[j] *= H0;
+      for (int kk = cnt - 1; kk >= 0; --kk) {
+        int i = lb_idx - 1 - kk;
+        if (i < 0) i += mem;
+        double rho = s_ra[i];
+        if (isnan(rho)) continue;
+        double sv[NQ], yv[NQ];
+#pragma unroll
+        for (int j = 0; j < NQ; ++j) {
+          sv[j] = own[j] ? tv(T.LS + i * T.np, l + G * j) : 0.0;
+          yv[j] = own[j] ? tv(T.LY + i * T.np, l + G * j) : 0.0;
+        }
+        double yq = 0.0;
+#pragma unroll
+        for (int j = 0; j < NQ; ++j)
+          if (own[j]) yq += yv[j] * q[j];
+        yq = tsum(yq);
+        double coef = s_ra[mem + i] - rho * yq;
+#pragma unroll
+        for (int j = 0; j < NQ; ++j)
+          if (own[j]) q[j] += coef * sv[j];
+      }
+#pragma unroll
+      for (int j = 0; j < NQ; ++j)
+        if (own[j]) tv(T.Q, l + G * j) = q[j];
+      return;
     }
     for (int kk = 0; kk < cnt; ++kk) {
       int i = lb_idx - 1 - kk;
@@ -302,11 +386,28 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       Vec XN = WL(M.X(nb), l);
       if (c_fb) {
         Vec XH = WL(M.XH(cb), cl);
-        for (int i = 0; i < n; ++i) XN.set(i, XH(i));
+        for (int i0 = 0; i0 < n; i0 += 8) {
+          double v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = i0 + k < n ? XH(i0 + k) : 0.0;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) if (i0 + k < n) XN.set(i0 + k, v[k]);
+        }
       } else {
         const double tau = ldexp(1.0, -c_idx);
         Vec X = WL(M.X(cb), cl), P = WL(M.P(cb), cl);
-        for (int i = 0; i < n; ++i) XN.set(i, X(i) + (1.0 - tau) * P(i) + tau * tv(T.Q, i));
+        for (int i0 = 0; i0 < n; i0 += 8) {  // loads first, stores after (see prox)
+          double xv[8], pv[8], qv[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const bool in = i0 + k < n;
+            xv[k] = in ? X(i0 + k) : 0.0;
+            pv[k] = in ? P(i0 + k) : 0.0;
+            qv[k] = in ? tv(T.Q, i0 + k) : 0.0;
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) if (i0 + k < n) XN.set(i0 + k, xv[k] + (1.0 - tau) * pv[k] + tau * qv[k]);
+        }
       }
       evp = XN; evg = WL(M.G(nb), l); want = 2;
     }
@@ -629,12 +730,25 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
               if (nJ > 0 && nJ < n) {
                 const double hf = 6.0554544523933395e-06 * (1.0 + sqrt(xx));
                 Vec XE = WL(M.XH(nb), l);
-                for (int i = 0; i < n; ++i) {
-                  double xi = Xj(i);
-                  double gd = fma(-gam, Gj(i), xi);
-                  bool active = gd < lbv[i] || ubv[i] < gd;
-                  double t = gd < lbv[i] ? lbv[i] : (gd > ubv[i] ? ubv[i] : gd);
-                  XE.set(i, fma(hf, active ? t - xi : 0.0, xi));
+                for (int i0 = 0; i0 < n; i0 += 8) {  // loads first, stores after (see prox)
+                  double xv[8], gv[8];
+#pragma unroll
+                  for (int k = 0; k < 8; ++k) {
+                    const bool in = i0 + k < n;
+                    xv[k] = in ? Xj(i0 + k) : 0.0;
+                    gv[k] = in ? Gj(i0 + k) : 0.0;
+                  }
+#pragma unroll
+                  for (int k = 0; k < 8; ++k) {
+                    const int i = i0 + k;
+                    if (i < n) {
+                      double xi = xv[k];
+                      double gd = fma(-gam, gv[k], xi);
+                      bool active = gd < lbv[i] || ubv[i] < gd;
+                      double t = gd < lbv[i] ? lbv[i] : (gd > ubv[i] ? ubv[i] : gd);
+                      XE.set(i, fma(hf, active ? t - xi : 0.0, xi));
+                    }
+                  }
                 }
                 evp = XE; evg = WL(M.P(nb), l); want = 2; fd_done = true; spec_for = target;
                 c_started = false;  // this lane's own x̂+, p+ rows now hold the speculation
