@@ -108,7 +108,16 @@ def oracle_setup(N, S=100):
     return orc, d, orc.default_solver_params(N)
 
 
+def host_threads():
+    """All host cores this process may use (torchrun exports OMP_NUM_THREADS=1: the oracle gets the count explicitly)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 def run_oracle(orc, d, sp, w, sample, threads=0):
+    threads = threads or host_threads()
     t0 = time.perf_counter()
     r = orc.solve(d, sp, w["x0"][:sample], w["road"], w["U0"][:sample], road_idx=w["road_idx"][:sample],
                   threads=threads, want_times=True)
@@ -145,7 +154,7 @@ def main_reference(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(B, N), "note": "alpaqa/CasADi are not installable here "
                        "(SURVEY §8c): the reference arm is the repo's C++ oracle of the same canonical solver spec"},
-            "cpu_baseline": {"value": v, "unit": "solves/s", "cores": orc.num_threads(), "kind": "port",
+            "cpu_baseline": {"value": v, "unit": "solves/s", "cores": host_threads(), "kind": "port",
                              "sample": f"first {sample} instances of the workload per step, OpenMP dynamic over instances"},
             "p50_solve_latency_ms": 1e3 * float(np.median(lat)),
             "e2e": {"value": v, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -243,7 +252,7 @@ def main_gpu(args, rank, local_rank, world):
     alg_bytes = B * (6 * 8 + 2 * N * 8 * 2 + 4 + 4 * 4 + 2 * 8 + 4 * 4)  # x0, U in/out, road_idx, status/iters/evals, psi/res
     roofline = {"bound": "fp64", "kernel": "k_eval_requests<Pacejka6>" if rounds_mode else "k_solve<Pacejka6>",
                 "achieved": achieved, "peak": peak_tflops,
-                "unit": "TFLOP/s", "frac": achieved / peak_tflops, "traffic": None,
+                "unit": "TFLOP/s", "frac": achieved / peak_tflops, "traffic": _ncu_traffic(rounds_mode),
                 "launches_per_step": n_k_launches, "avg_launch_ms": k_ms / max(n_k_launches, 1),
                 "flop_per_launch": alg_flops / max(n_k_launches, 1),
                 "kernel_share_of_step": k_ms / float(step_ms[-1]),
@@ -302,7 +311,7 @@ def main_gpu(args, rank, local_rank, world):
         orc, d, sp = oracle_setup(N)
         sample = args.cpu_sample or cpu_sample_size(orc, d, sp, w, B)
         t, r = run_oracle(orc, d, sp, w, sample)
-        cpu = {"value": sample / t, "unit": "solves/s", "cores": orc.num_threads(), "kind": "port",
+        cpu = {"value": sample / t, "unit": "solves/s", "cores": host_threads(), "kind": "port",
                "sample": f"first {sample} instances of the same workload, OpenMP over instances",
                "p50_solve_latency_ms": 1e3 * float(np.median(r["times"]))}
 
@@ -326,6 +335,18 @@ def main_gpu(args, rank, local_rank, world):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _ncu_traffic(rounds_mode):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu capture (one bulk-phase
+    launch; profiles/r01_ncu_traffic.json says which), or None."""
+    if not rounds_mode:
+        return None
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))
+        return {"dram_bytes_per_launch": t["dram_bytes_per_launch"], "of": t["capture"], "note": t["note"]}
+    except Exception:
+        return None
 
 
 def _hbm_peak():

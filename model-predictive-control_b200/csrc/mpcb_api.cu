@@ -7,6 +7,9 @@
 #include <cstring>
 #include <limits>
 #include <string>
+#include <algorithm>
+#include <utility>
+#include <vector>
 #include "mpcb_kernels.cuh"
 #include "mpcb_solve.cuh"
 
@@ -482,11 +485,19 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
       CK(cudaMemcpyToSymbolAsync(g_dbg_calls, z, sizeof(z), 0, cudaMemcpyHostToDevice, st));
     }
     std::FILE* log = h->round_log ? std::fopen(h->round_log, "w") : nullptr;
+    // MPCB_EVAL_TRACE=r: per-chunk cycle counts of evaluation launch r, printed to stderr (diagnostic)
+    long long trace_round = -1;
+    if (const char* tr = std::getenv("MPCB_EVAL_TRACE")) {
+      trace_round = std::atoll(tr);
+      if ((rc = grow(h, &h->dbg, &h->dbg_cap, (size_t)(ns / 32 + 2) * 2 * sizeof(long long), st))) return rc;
+      CK(cudaMemsetAsync(h->dbg, 0, (size_t)(ns / 32 + 2) * 2 * sizeof(long long), st));
+    }
     h->last_eval_ms = 0.0; h->last_trans_ms = 0.0;
     for (;;) {
       for (int i = 0; i < chunk; ++i, ++round) {
         a.round = (int)round;
         e.counters = h->rs_counters + 4 * (round & 1);
+        e.trace = (trace_round >= 0 && round == trace_round) ? (long long*)h->dbg : nullptr;
         CK(cudaEventRecord(h->rs_ev[3 * i], st));
         if (k.model_id == MPCB_MODEL_PACEJKA6) {
           MPCB_LAUNCH_T_G(MPCB_MODEL_PACEJKA6)
@@ -512,6 +523,28 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
         h->last_trans_ms += t1; h->last_eval_ms += t2;
         if (log) std::fprintf(log, "%lld %u %u %.4f %.4f\n", (long long)(round - chunk + i), h->rs_counters_host[4 * i],
                               h->rs_counters_host[4 * i + 1], t1, t2);
+      }
+      if (trace_round >= 0 && trace_round < round && trace_round >= round - chunk) {
+        const int i = (int)(trace_round - (round - chunk));
+        (void)i;
+        std::vector<long long> tr((size_t)(ns / 32 + 2) * 2);
+        CK(cudaMemcpy(tr.data(), h->dbg, tr.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+        std::vector<std::pair<long long, long long>> v;
+        for (size_t c = 0; c < tr.size() / 2; ++c) if (tr[2 * c] > 0) v.push_back({tr[2 * c], (long long)c});
+        std::sort(v.begin(), v.end());
+        if (!v.empty()) {
+          std::fprintf(stderr, "[mpcb trace] round %lld: %zu chunks, cycles min %lld median %lld p90 %lld max %lld\n", trace_round,
+                       v.size(), v.front().first, v[v.size() / 2].first, v[v.size() * 9 / 10].first, v.back().first);
+          long long nf_chunks = 0, nf_cyc = 0, ok_cyc = 0;
+          for (auto& w : v) { if (tr[2 * w.second + 1] % 1000) { ++nf_chunks; nf_cyc += w.first; } else ok_cyc += w.first; }
+          std::fprintf(stderr, "[mpcb trace]   chunks with a non-finite psi: %lld (mean cycles %lld), without: %zu (mean cycles %lld)\n",
+                       nf_chunks, nf_chunks ? nf_cyc / nf_chunks : 0, v.size() - (size_t)nf_chunks,
+                       v.size() > (size_t)nf_chunks ? ok_cyc / (long long)(v.size() - nf_chunks) : 0);
+          for (size_t k = 0; k < 8 && k < v.size(); ++k) {
+            const auto& w = v[v.size() - 1 - k];
+            std::fprintf(stderr, "[mpcb trace]   chunk %lld cycles %lld kind+nonfinite lanes %lld\n", w.second, w.first, tr[2 * w.second + 1]);
+          }
+        }
       }
       const unsigned* last = h->rs_counters_host + 4 * (chunk - 1);
       if (last[0] == 0 && last[1] == 0) break;

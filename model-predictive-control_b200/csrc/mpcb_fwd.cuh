@@ -377,7 +377,7 @@ __device__ __noinline__ void stage_fm(double* pq, double ud, double udl, Vec scr
 // (stage_problem()).
 template <int MODEL, bool GRAD>
 __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, Vec U, Vec scr, Vec grad, bool store,
-                                       Vec states = Vec{nullptr, 0}, IVec idx_out = IVec{nullptr, 0}) {
+                                       Vec states = Vec{nullptr, 0}, IVec idx_out = IVec{nullptr, 0}, bool cut = false) {
   const KDesc& d = s_desc;
   using M = Fm<MODEL>;
   constexpr int NX = M::NX, ND = M::ND, K = fm_stage_doubles<MODEL>();
@@ -386,11 +386,25 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
   for (int i = 0; i < NX; ++i) y[i] = x0[i];
   double cost = 0.0;
   int idx = -1;  // nearest vertex of the previous stage: where the next search starts
+  // `cut` (the solver's evaluations only): a lane whose state left every sane range (NaN, or a component beyond
+  // 1e100: psi would be NaN, Inf or > 1e200) stops here with psi = NaN and a NaN gradient.  Only line-search points
+  // x + (1 - tau) p + tau q can do that (they are not box-feasible) and PANOC rejects them whichever of the three
+  // psi is, so the iterates are unchanged; without the cut such a lane kept its whole warp in the slow routes of
+  // the model call, the vertex scan and wrap_to_pi for the rest of the horizon (2.4x the time of a normal chunk,
+  // and an evaluation launch lasts as long as its slowest chunk: profiles/r01_round_mode.md).
+  bool dead = false;
 #pragma unroll 1
   for (int n = 0; n < d.N; ++n) {
+    if (dead) continue;
     const double ud = U(2 * n), udl = U(2 * n + 1);
     const int o = n * K;
     stage_fm<MODEL, GRAD>(y, ud, udl, scr, o, store);
+    if (cut) {
+      bool sane = true;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) sane = sane && fabs(y[i]) < 1e100;
+      if (!sane) { dead = true; continue; }
+    }
     double gy[NX], gu[2];
     cost += stage_cost<MODEL, GRAD, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
     if (states.p) {
@@ -402,6 +416,14 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
 #pragma unroll
       for (int i = 0; i < NX; ++i) scr.set(o + NX * ND + 2 + i, gy[i]);
     }
+  }
+  if (dead) {
+    const double nn = nan("");
+    if (GRAD && store)
+      for (int i = 0; i < 2 * d.N; ++i) grad.set(i, nn);
+    if (states.p)
+      for (int i = 0; i < d.N * NX; ++i) states.set(i, nn);
+    return nn;
   }
   if (GRAD && store) {
     // horizon adjoint over the stored stage Jacobians

@@ -939,8 +939,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       for (int i = 0; i < NX; ++i) y0[i] = a.x0[b * NX + i];
       const Vec scr = WL(M.SCR, l);
       const Vec stv = want == 3 ? WL(M.ST, l) : Vec{nullptr, 0};
-      if (anyg) val = eval_fm<MODEL, true>(r, ex, y0, evp, scr, evg, want == 2, stv);
-      else val = eval_fm<MODEL, false>(r, ex, y0, evp, scr, evg, false, stv);
+      if (anyg) val = eval_fm<MODEL, true>(r, ex, y0, evp, scr, evg, want == 2, stv, IVec{nullptr, 0}, true);
+      else val = eval_fm<MODEL, false>(r, ex, y0, evp, scr, evg, false, stv, IVec{nullptr, 0}, true);
       if (want == 2) ++n_grad;
       else if (want == 1) ++n_val;
     }
@@ -974,6 +974,7 @@ struct EvalArgs {
   const int32_t *list_grad, *list_val;
   unsigned* counters;       // this round's [4]
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
+  long long* trace;         // diagnostic (MPCB_EVAL_TRACE=round): per chunk [cycles, first slot] or null
 };
 
 // Launch shape: ONE CTA of 256 lanes per SM, so a CTA's warps w and w + 4 share an SM sub-partition and
@@ -1010,6 +1011,8 @@ k_eval_requests(KDesc d, EvalArgs e) {
     if (c >= cg + cv) break;
     const bool grad = c < cg;
     const unsigned idx = ((grad ? c : c - cg) << 5) + (unsigned)lane;
+    const long long t_chunk = e.trace ? clock64() : 0;
+    bool nonfinite = false;
     if (idx < (grad ? ng : nv)) {
       const int64_t slot = grad ? e.list_grad[idx] : e.list_val[idx];
       const int want = e.req_want[slot];
@@ -1024,11 +1027,20 @@ k_eval_requests(KDesc d, EvalArgs e) {
       const Vec pt{e.req_p[slot], e.ns};
       const Vec out{e.req_g[slot], e.ns};
       double v;
-      if (grad) v = eval_fm<MODEL, true>(r, ex, y0, pt, scr, out, true, Vec{nullptr, 0});
-      else v = eval_fm<MODEL, false>(r, ex, y0, pt, scr, Vec{nullptr, 0}, false, want == 3 ? out : Vec{nullptr, 0});
+      if (grad) v = eval_fm<MODEL, true>(r, ex, y0, pt, scr, out, true, Vec{nullptr, 0}, IVec{nullptr, 0}, true);
+      else v = eval_fm<MODEL, false>(r, ex, y0, pt, scr, Vec{nullptr, 0}, false, want == 3 ? out : Vec{nullptr, 0},
+                                     IVec{nullptr, 0}, true);
       e.req_val[slot] = v;
+      nonfinite = !(fabs(v) < 1e300);
     }
     __syncwarp();
+    if (e.trace) {
+      const unsigned nf = __ballot_sync(0xffffffffu, nonfinite);
+      if (lane == 0) {
+        e.trace[2 * c] = clock64() - t_chunk;
+        e.trace[2 * c + 1] = (grad ? 1000 : 0) + __popc(nf);  // lanes whose psi came out NaN / Inf / > 1e300
+      }
+    }
   }
 }
 
