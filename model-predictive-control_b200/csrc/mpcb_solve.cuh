@@ -104,6 +104,17 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   if constexpr (!ROUND) {
     fm_load_smem();
     if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
+  } else if (a.round > 0) {
+    // a CTA whose tiles have all finished leaves before any staging: late in a batch a handful of tiles is
+    // alive and the launch is thousands of such CTAs
+    const int64_t s0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (__syncthreads_and((a.si[s0] & 1024) != 0)) {
+      if (s0 == 0) {
+        unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
+        nx[0] = 0u; nx[1] = 0u; nx[2] = 0u;
+      }
+      return;
+    }
   }
   for (int i = threadIdx.x; i < n; i += blockDim.x) { sbox[i] = a.lb[i]; sbox[n + i] = a.ub[i]; }
   if constexpr (ROUND) __syncthreads();

@@ -114,6 +114,42 @@ def test_rollout_and_gradient_parity(mp, orc, model, N):
     assert np.median(gerr) < 1e-11 and gerr.max() < 1e-7
 
 
+def test_wide_route_and_unbounded_inputs_parity(mp, orc):
+    """Inputs far outside the box (what line-search points x + q look like): large slip angles, reversing, spin-outs —
+    the model call's wide route (atan by selects, atan2's left half-plane) against the oracle's libm, and blow-ups.
+    The public rollout / value_grad entry points do not cut blown-up instances: non-finite costs appear exactly where
+    the oracle's do; finite ones agree (short horizon: the dynamics amplify rounding quickly out here)."""
+    from mpcb200 import workloads as wl
+    B, N, S = 512, 6, 100
+    w = wl.tracking_batch(B, N, S, seed=808)
+    rng = np.random.default_rng(808)
+    U = np.empty((B, 2 * N))
+    U[:, 0::2] = rng.uniform(-6, 6, (B, N))       # box is [-1, 1]
+    U[:, 1::2] = rng.uniform(-2.5, 2.5, (B, N))   # box is [-0.32, 0.32]
+    U[:8, 0::2] = -2000.0                         # exponential blow-up of vx within the horizon
+    x0 = w["x0"].copy()
+    x0[8:40, 3] = rng.uniform(-1.5, -0.2, 32)     # reversing from the start
+    prob = mp.BatchedMpc(N=N, S=S, road_mode=mp.ROAD_TABLE, n_roads=2)
+    d = _desc(orc, 0, N, S, 1, 2)
+    _, _, cost = prob.rollout(x0, U, w["road"], road_idx=w["road_idx"])
+    _, _, cost_r = orc.rollout(d, x0, U, w["road"], road_idx=w["road_idx"])
+    c, g = prob.value_grad(x0, U, w["road"], road_idx=w["road_idx"])
+    c_r, g_r = orc.value_grad(d, x0, U, w["road"], road_idx=w["road_idx"])
+    cost, c, g = cost.cpu().numpy(), c.cpu().numpy(), g.cpu().numpy()
+    fin = np.isfinite(cost_r) & (np.abs(cost_r) < 1e100)
+    assert fin.sum() > 0.9 * (B - 8) and not fin[:8].any()
+    assert (np.isfinite(cost) & (np.abs(cost) < 1e100) == fin).all()
+    rel = np.abs(cost[fin] - cost_r[fin]) / np.abs(cost_r[fin])
+    relc = np.abs(c[fin] - c_r[fin]) / np.abs(c_r[fin])
+    scale = np.abs(g_r[fin]).max(axis=1)
+    gerr = np.abs(g[fin] - g_r[fin]).max(axis=1) / scale
+    print(f"unbounded inputs: finite {fin.mean():.3f}; cost rel err median {np.median(rel):.1e} p99 {np.quantile(rel, .99):.1e} "
+          f"max {rel.max():.1e}; grad err median {np.median(gerr):.1e} p99 {np.quantile(gerr, .99):.1e}")
+    assert np.median(rel) < 1e-12 and np.quantile(rel, 0.99) < 1e-8
+    assert np.median(relc) < 1e-12 and np.quantile(relc, 0.99) < 1e-8
+    assert np.median(gerr) < 1e-10 and np.quantile(gerr, 0.95) < 1e-6
+
+
 def test_road_modes_agree(mp, orc):
     """shared / table / per-instance / Bezier layouts give identical results for identical polylines."""
     from mpcb200 import workloads as wl
