@@ -462,6 +462,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     e.x0 = x0; e.p = p; e.obs = obs; e.lam = lambda; e.sig_base = h->wst + (size_t)TM.SIG * nt; e.ra = ra;
     e.req_want = a.req_want; e.req_b = a.req_b; e.req_p = a.req_p; e.req_g = a.req_g; e.req_val = a.req_val;
     e.list_grad = a.list_grad; e.list_val = a.list_val; e.escr = h->rs_escr;
+    e.split_ok = 1;
+    if (const char* sv = std::getenv("MPCB_SPLIT")) e.split_ok = std::atoi(sv) != 0;
 #define MPCB_LAUNCH_T(MODEL, GG)                                                               \
   do {                                                                                         \
     if (round == 0 && (rc = set_smem(h, k_solve<MODEL, GG, true>, box_smem))) return rc;       \

@@ -217,6 +217,22 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
   static MPCB_DEV void seed(double* tq) {
     tq[0] = 0.0; tq[1] = J == 0 ? 1.0 : 0.0; tq[2] = J == 1 ? 1.0 : 0.0; tq[3] = J == 2 ? 1.0 : 0.0;
   }
+  // the same with the direction as a run-time value (split evaluation: one direction per lane)
+  static MPCB_DEV void tan_rt(const Lin& L, const double* tq, int J, double* tkp, double* tkq) {
+    tkp[0] = fma(L.c, tq[1], fma(-L.s, tq[2], -L.f1 * tq[0]));
+    tkp[1] = fma(L.s, tq[1], fma(L.c, tq[2], L.f0 * tq[0]));
+    tkq[0] = tq[3];
+    double k1 = fma(L.a11, tq[1], fma(L.a12, tq[2], L.a13 * tq[3]));
+    double k2 = fma(L.a21, tq[1], fma(L.a22, tq[2], L.a23 * tq[3]));
+    double k3 = fma(L.a31, tq[1], fma(L.a32, tq[2], L.a33 * tq[3]));
+    k1 += J == 3 ? L.bd : (J == 4 ? L.bl1 : 0.0);
+    k2 += J == 4 ? L.bl2 : 0.0;
+    k3 += J == 4 ? L.bl3 : 0.0;
+    tkq[1] = k1; tkq[2] = k2; tkq[3] = k3;
+  }
+  static MPCB_DEV void seed_rt(double* tq, int J) {
+    tq[0] = 0.0; tq[1] = J == 0 ? 1.0 : 0.0; tq[2] = J == 1 ? 1.0 : 0.0; tq[3] = J == 2 ? 1.0 : 0.0;
+  }
 };
 
 // ---- Kinematic-4 (dynamics.py:144-173): q = (phi, v), directions v, d, delta ---------------------
@@ -250,6 +266,17 @@ template <> struct Fm<MPCB_MODEL_KINEMATIC4> {
   }
   template <int J>
   static MPCB_DEV void seed(double* tq) { tq[0] = 0.0; tq[1] = J == 0 ? 1.0 : 0.0; }
+  static MPCB_DEV void tan_rt(const Lin& L, const double* tq, int J, double* tkp, double* tkq) {
+    double ta = tq[0] + (J == 2 ? L.db : 0.0);
+    tkp[0] = fma(L.c, tq[1], -L.v * L.s * ta);
+    tkp[1] = fma(L.s, tq[1], L.v * L.c * ta);
+    double k0 = tq[1] * L.sb_lr;
+    k0 = J == 2 ? fma(L.v, L.cb_lr_db, k0) : k0;
+    double k1 = -L.mu * tq[1];
+    k1 += J == 1 ? L.acc : 0.0;
+    tkq[0] = k0; tkq[1] = k1;
+  }
+  static MPCB_DEV void seed_rt(double* tq, int J) { tq[0] = 0.0; tq[1] = J == 0 ? 1.0 : 0.0; }
 };
 
 // Compile-time loop over tangent directions (J must be a constant inside Fm::tan / Fm::seed).
@@ -451,6 +478,150 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
 #pragma unroll
       for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
     }
+  }
+  return cost;
+}
+
+// ---- split evaluation: one tangent direction per lane -------------------------------------------------
+// A lone warp issues one DFMA per 3.75 cycles, so the psi + grad psi evaluation of ONE request is bound by its
+// own instruction count (389 fp64 instructions per model call with all 5 tangents, 1 357 cycles) even when the
+// GPU is otherwise idle — the state of the last rounds of every batch.  When few gradient requests are left a
+// group of 8 lanes shares a request: every lane carries the primal (identical arithmetic, identical results)
+// and ONE tangent direction J = lane % 8 (lanes J >= ND idle along), which cuts the instruction stream of a
+// model call to primal + one tangent.  The group leader (J = 0) owns the stage-Jacobian scratch column the
+// lanes write their Jacobian columns to, and runs the horizon adjoint.
+template <int MODEL>
+MPCB_DEV void rk4_fm_split(double* p, double* q, double* tp, double* tq, int J, const StageU& su, const VehP& v, double h) {
+  using M = Fm<MODEL>;
+  constexpr int NQ = M::NQ;
+  const double h6 = h * (1.0 / 6.0);
+  double kp[2] = {0.0, 0.0}, kq[NQ], accp[2] = {0.0, 0.0}, accq[NQ], tkq[NQ], taq[NQ];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) { kq[i] = 0.0; accq[i] = 0.0; tkq[i] = 0.0; taq[i] = 0.0; }
+#pragma unroll 1
+  for (int s = 0; s < 4; ++s) {
+    const double a = s == 0 ? 0.0 : (s == 3 ? h : 0.5 * h);
+    const double bw = (s == 0 || s == 3) ? 1.0 : 2.0;
+    double sq[NQ];
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) sq[i] = fma(a, kq[i], q[i]);
+    typename M::Lin L;
+    M::template call<true>(sq, su, v, kp, kq, L);
+    accp[0] = fma(bw, kp[0], accp[0]);
+    accp[1] = fma(bw, kp[1], accp[1]);
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) accq[i] = fma(bw, kq[i], accq[i]);
+    const double wp = bw * h6;
+    double tsq[NQ], tkp[2], tk[NQ];
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) tsq[i] = fma(a, tkq[i], tq[i]);
+    M::tan_rt(L, tsq, J, tkp, tk);
+    tp[0] = fma(wp, tkp[0], tp[0]);
+    tp[1] = fma(wp, tkp[1], tp[1]);
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) { tkq[i] = tk[i]; taq[i] = fma(bw, tk[i], taq[i]); }
+  }
+  p[0] = fma(h6, accp[0], p[0]);
+  p[1] = fma(h6, accp[1], p[1]);
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) q[i] = fma(h6, accq[i], q[i]);
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) tq[i] = fma(h6, taq[i], tq[i]);
+}
+
+template <int MODEL>
+__device__ __noinline__ void stage_fm_split(double* pq, double ud, double udl, Vec scr, int o, int J) {
+  using M = Fm<MODEL>;
+  constexpr int NX = M::NX, NQ = M::NQ, ND = M::ND;
+  const VehP& v = s_veh;
+  StageU su;
+  make_stage_u<MODEL>(su, ud, udl, v, true);
+  double p[2] = {pq[0], pq[1]}, q[NQ];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) q[i] = pq[2 + i];
+  double tp[2] = {0.0, 0.0}, tq[NQ];
+  M::seed_rt(tq, J);
+  const double px0 = p[0], py0 = p[1];
+  const int n_sub = s_desc.n_sub;
+  const double h = s_desc.h;
+#pragma unroll 1
+  for (int e = 0; e < n_sub; ++e) rk4_fm_split<MODEL>(p, q, tp, tq, J, su, v, h);
+  pq[0] = p[0]; pq[1] = p[1];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) pq[2 + i] = q[i];
+  if (J < ND) {
+    scr.set(o + J * NX, tp[0]);
+    scr.set(o + J * NX + 1, tp[1]);
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) scr.set(o + J * NX + 2 + i, tq[i]);
+  }
+  if (J == 0) {
+    scr.set(o + NX * ND, p[0] - px0);
+    scr.set(o + NX * ND + 1, p[1] - py0);
+  }
+}
+
+// psi + grad psi of one request by a group of 8 lanes (all of them call this; `scr` is the LEADER's scratch
+// column, J = lane % 8).  The gradient is written by the leader; every lane returns psi.  Same cut as eval_fm.
+template <int MODEL>
+__device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double* x0, Vec U, Vec scr, Vec grad, int J,
+                                             unsigned gmask) {
+  const KDesc& d = s_desc;
+  using M = Fm<MODEL>;
+  constexpr int NX = M::NX, ND = M::ND, K = fm_stage_doubles<MODEL>();
+  double y[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) y[i] = x0[i];
+  double cost = 0.0;
+  int idx = -1;
+  bool dead = false;
+#pragma unroll 1
+  for (int n = 0; n < d.N; ++n) {
+    if (dead) continue;
+    const double ud = U(2 * n), udl = U(2 * n + 1);
+    const int o = n * K;
+    stage_fm_split<MODEL>(y, ud, udl, scr, o, J);
+    bool sane = true;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) sane = sane && fabs(y[i]) < 1e100;
+    if (!sane) { dead = true; continue; }
+    double gy[NX], gu[2];
+    cost += stage_cost<MODEL, true, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
+    if (J == 0) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) scr.set(o + NX * ND + 2 + i, gy[i]);
+    }
+  }
+  __syncwarp(gmask);  // the columns written by the other lanes of the group are visible to the leader
+  if (J != 0) return dead ? nan("") : cost;
+  if (dead) {
+    const double nn = nan("");
+    for (int i = 0; i < 2 * d.N; ++i) grad.set(i, nn);
+    return nn;
+  }
+  double lam[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) lam[i] = 0.0;
+#pragma unroll 1
+  for (int n = d.N - 1; n >= 0; --n) {
+    const int o = n * K;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) lam[i] += scr(o + NX * ND + 2 + i);
+    double dots[ND];
+#pragma unroll
+    for (int j = 0; j < ND; ++j) {
+      double s = 0.0;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) s = fma(scr(o + j * NX + i), lam[i], s);
+      dots[j] = s;
+    }
+    const double dx = scr(o + NX * ND), dy = scr(o + NX * ND + 1);
+    const double ud = U(2 * n), udl = U(2 * n + 1);
+    grad.set(2 * n, fma(2.0 * d.c[5], ud, dots[ND - 2]));
+    grad.set(2 * n + 1, fma(2.0 * d.c[4], udl, dots[ND - 1]));
+    lam[2] = lam[2] - dy * lam[0] + dx * lam[1];
+#pragma unroll
+    for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
   }
   return cost;
 }

@@ -986,6 +986,7 @@ struct EvalArgs {
   unsigned* counters;       // this round's [4]
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
   long long* trace;         // diagnostic (MPCB_EVAL_TRACE=round): per chunk [cycles, first slot] or null
+  int split_ok;             // 0: never use the split evaluation (MPCB_SPLIT=0)
 };
 
 // Launch shape: ONE CTA of 256 lanes per SM, so a CTA's warps w and w + 4 share an SM sub-partition and
@@ -1007,8 +1008,13 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const int64_t eslot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const Vec scr{e.escr + eslot, e.ens};
   const unsigned ng = e.counters[0], nv = e.counters[1];
-  const unsigned cg = (ng + 31u) >> 5, cv = (nv + 31u) >> 5;
   const unsigned n_warps = gridDim.x * (blockDim.x >> 5);
+  const unsigned cv = (nv + 31u) >> 5;
+  // few gradient requests (every chunk still gets a warp slot of its own on half the sub-partitions): 8 lanes per
+  // request, one tangent direction each (eval_fm_split) — the latency floor of a round drops with the
+  // per-warp instruction count
+  const bool split = e.split_ok && ng > 0 && ((ng + 3u) >> 2) + cv <= (n_warps >> 1);
+  const unsigned cg = split ? (ng + 3u) >> 2 : (ng + 31u) >> 5;
   bool first = true;
   for (;;) {
     unsigned c = 0;
@@ -1024,7 +1030,26 @@ k_eval_requests(KDesc d, EvalArgs e) {
     const unsigned idx = ((grad ? c : c - cg) << 5) + (unsigned)lane;
     const long long t_chunk = e.trace ? clock64() : 0;
     bool nonfinite = false;
-    if (idx < (grad ? ng : nv)) {
+    if (grad && split) {
+      const int J = lane & 7;
+      const unsigned ridx = (c << 2) + (unsigned)(lane >> 3);
+      if (ridx < ng) {
+        const int64_t slot = e.list_grad[ridx];
+        const int64_t b = e.req_b[slot];
+        const int64_t tile = slot / e.G;
+        RoadView r = road_view(e.ra, sroad, d.S, b);
+        Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
+                  d.bounded ? e.sig_base + tile : nullptr, 1, e.nt};
+        double y0[NX];
+#pragma unroll
+        for (int i = 0; i < NX; ++i) y0[i] = e.x0[b * NX + i];
+        const Vec scr_lead{e.escr + (eslot - J), e.ens};
+        const double v = eval_fm_split<MODEL>(r, ex, y0, Vec{e.req_p[slot], e.ns}, scr_lead, Vec{e.req_g[slot], e.ns}, J,
+                                              0xffu << (lane & 24));
+        if (J == 0) e.req_val[slot] = v;
+        nonfinite = J == 0 && !(fabs(v) < 1e300);
+      }
+    } else if (idx < (grad ? ng : nv)) {
       const int64_t slot = grad ? e.list_grad[idx] : e.list_val[idx];
       const int want = e.req_want[slot];
       const int64_t b = e.req_b[slot];

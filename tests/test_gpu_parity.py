@@ -313,6 +313,36 @@ def test_round_mode_equals_persistent_mode(mp, G, bounded, monkeypatch):
         np.testing.assert_allclose(l0[same], l1[same], rtol=1e-6, atol=1e-9)
 
 
+@pytest.mark.parametrize("model", [0, 1])
+def test_split_evaluation_equals_full_evaluation(mp, model, monkeypatch):
+    """Round mode evaluates the gradient requests of thin rounds with 8 lanes per request, one tangent direction per
+    lane (eval_fm_split, MPCB_SPLIT=0 turns it off): same arithmetic per direction, so the same iterates."""
+    from mpcb200 import workloads as wl
+    N, B, S = 20, 96, 100
+    monkeypatch.setenv("MPCB_MODE", "rounds")
+    out = {}
+    for split in ("0", "1"):
+        monkeypatch.setenv("MPCB_SPLIT", split)
+        if model == 0:
+            w = wl.tracking_batch(B, N, S, seed=77)
+            prob = mp.BatchedMpc(N=N, S=S, road_mode=mp.ROAD_TABLE, n_roads=2)
+            U, _, st = prob.solve(w["x0"], w["road"], w["U0"].copy(), road_idx=w["road_idx"])
+        else:
+            lc = wl.lane_change_batch(B, N, S, seed=78, n_obs=2)
+            prob = mp.BatchedMpc(N=N, S=S, model_id=1, road_mode=mp.ROAD_BEZIER, flags=mp.FLAG_LANE | mp.FLAG_OBST,
+                                 n_obs=2, v_ref=20.0)
+            U, _, st = prob.solve(lc["x0"], lc["ctrl"], lc["U0"].copy(), obs=lc["obs"])
+        out[split] = (U.cpu().numpy(), st)
+    (U0, s0), (U1, s1) = out["0"], out["1"]
+    it0, it1 = s0.inner_iterations.cpu().numpy(), s1.inner_iterations.cpu().numpy()
+    same = it0 == it1
+    print(f"model {model}: identical inner-iteration counts {same.mean():.3f}, bit-identical U {np.mean((U0 == U1).all(axis=1)):.3f}, "
+          f"max |dU| {np.abs(U0 - U1)[same].max():.2e}")
+    assert (s0.status.cpu().numpy() == s1.status.cpu().numpy()).all()
+    assert same.mean() > 0.95
+    assert np.abs(U0 - U1)[same].max() < 1e-7
+
+
 def test_solve_host_equals_solve_device(mp, orc):
     from mpcb200 import workloads as wl
     N, B = 12, 100
