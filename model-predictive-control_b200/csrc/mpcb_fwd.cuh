@@ -420,10 +420,12 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
   // the model call, the vertex scan and wrap_to_pi for the rest of the horizon (2.4x the time of a normal chunk,
   // and an evaluation launch lasts as long as its slowest chunk: profiles/r01_round_mode.md).
   bool dead = false;
+  double ud_next = U(0), udl_next = U(1);  // the next stage's inputs are requested one stage ahead (DRAM latency)
 #pragma unroll 1
   for (int n = 0; n < d.N; ++n) {
     if (dead) continue;
-    const double ud = U(2 * n), udl = U(2 * n + 1);
+    const double ud = ud_next, udl = udl_next;
+    if (n + 1 < d.N) { ud_next = U(2 * n + 2); udl_next = U(2 * n + 3); }
     const int o = n * K;
     stage_fm<MODEL, GRAD>(y, ud, udl, scr, o, store);
     if (cut) {
@@ -575,10 +577,12 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
   double cost = 0.0;
   int idx = -1;
   bool dead = false;
+  double ud_next = U(0), udl_next = U(1);
 #pragma unroll 1
   for (int n = 0; n < d.N; ++n) {
     if (dead) continue;
-    const double ud = U(2 * n), udl = U(2 * n + 1);
+    const double ud = ud_next, udl = udl_next;
+    if (n + 1 < d.N) { ud_next = U(2 * n + 2); udl_next = U(2 * n + 3); }
     const int o = n * K;
     stage_fm_split<MODEL>(y, ud, udl, scr, o, J);
     bool sane = true;
