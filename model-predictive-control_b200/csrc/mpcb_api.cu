@@ -390,8 +390,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   // Tile width: spare lanes are spent on speculative line-search candidates (mpcb_solve.cuh).
   const int block = 64;
   // small batches: one asynchronous persistent launch; from a few thousand instances on the rounds win
-  // (profiles/r01_round_mode.md: 395 vs 413 ms at B = 4096, 2.8 vs 6.9 s at B = 65536)
-  const int mode = h->mode_override >= 0 ? h->mode_override : (B >= 2048 ? 1 : 0);
+  // (profiles/r01_round_mode.md: 218 vs 244 ms at B = 1024, 289 vs 413 ms at B = 4096, 2.6 vs 6.9 s at B = 65536)
+  const int mode = h->mode_override >= 0 ? h->mode_override : (B >= 1024 ? 1 : 0);
   const int64_t lane_cap = (int64_t)h->num_sms * h->warps_per_sm * 32;
   int G = 1;
   if (mode == 1) {

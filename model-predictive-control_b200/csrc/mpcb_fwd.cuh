@@ -413,10 +413,11 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
   for (int i = 0; i < NX; ++i) y[i] = x0[i];
   double cost = 0.0;
   int idx = -1;  // nearest vertex of the previous stage: where the next search starts
-  // `cut` (the solver's evaluations only): a lane whose state left every sane range (NaN, or a component beyond
-  // 1e100: psi would be NaN, Inf or > 1e200) stops here with psi = NaN and a NaN gradient.  Only line-search points
-  // x + (1 - tau) p + tau q can do that (they are not box-feasible) and PANOC rejects them whichever of the three
-  // psi is, so the iterates are unchanged; without the cut such a lane kept its whole warp in the slow routes of
+  // `cut` (the solver's evaluations only): a lane whose state holds a NaN, or a velocity component whose square
+  // overflows (the speed term of the cost is then +Inf, so psi is +Inf or NaN), stops here with psi = NaN and a NaN
+  // gradient.  Only line-search points x + (1 - tau) p + tau q can get there (they are not box-feasible) and PANOC
+  // rejects a point whose psi is +Inf exactly as one whose psi is NaN (phi+ is not finite, every test on it is
+  // false), so the iterates are unchanged; without the cut such a lane kept its whole warp in the slow routes of
   // the model call, the vertex scan and wrap_to_pi for the rest of the horizon (2.4x the time of a normal chunk,
   // and an evaluation launch lasts as long as its slowest chunk: profiles/r01_round_mode.md).
   bool dead = false;
@@ -431,7 +432,8 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
     if (cut) {
       bool sane = true;
 #pragma unroll
-      for (int i = 0; i < NX; ++i) sane = sane && fabs(y[i]) < 1e100;
+      for (int i = 0; i < NX; ++i) sane = sane && y[i] == y[i];
+      sane = sane && fabs(y[3]) < 1.3e154 && (MODEL == MPCB_MODEL_KINEMATIC4 || fabs(y[NX == 6 ? 4 : 3]) < 1.3e154);
       if (!sane) { dead = true; continue; }
     }
     double gy[NX], gu[2];
@@ -587,7 +589,8 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
     stage_fm_split<MODEL>(y, ud, udl, scr, o, J);
     bool sane = true;
 #pragma unroll
-    for (int i = 0; i < NX; ++i) sane = sane && fabs(y[i]) < 1e100;
+    for (int i = 0; i < NX; ++i) sane = sane && y[i] == y[i];
+    sane = sane && fabs(y[3]) < 1.3e154 && (MODEL == MPCB_MODEL_KINEMATIC4 || fabs(y[NX == 6 ? 4 : 3]) < 1.3e154);
     if (!sane) { dead = true; continue; }
     double gy[NX], gu[2];
     cost += stage_cost<MODEL, true, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
