@@ -559,10 +559,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     if (h->debug_timers >= 2) {
       unsigned long long c[8];
       if (cudaMemcpyFromSymbol(c, g_dbg_calls, sizeof(c)) == cudaSuccess)
-        if (h->debug_timers >= 5)
-          std::fprintf(stderr, "[mpcb debug] split evaluation, per stage (leader lanes): stage_fm_split %.0f cycles, stage_cost %.0f cycles, %llu stages\n",
-                       (double)c[0] / (double)(c[5] + 1), (double)c[1] / (double)(c[5] + 1), c[5]);
-        else std::fprintf(stderr, "[mpcb debug] model calls by lane: fast %llu wide %llu nan %llu slow %llu; warp calls %llu, "
+        std::fprintf(stderr, "[mpcb debug] model calls by lane: fast %llu wide %llu nan %llu slow %llu; warp calls %llu, "
                      "with a wide lane %llu, with a slow lane %llu\n", c[0], c[2], c[3], c[4], c[5], c[6], c[7]);
     }
     h->last_rounds = round;

@@ -158,14 +158,14 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     const double am = fmax(fabs(a_f), fabs(a_r));
     const bool ok = vx > 0x1p-960 && vx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX;
     const bool fast = ok && su.z2_mode == 2 && am <= 0.5 * vx;
-    if (s_desc.debug >= 2 && s_desc.debug < 5) atomicAdd(&g_dbg_calls[fast ? 0 : 1], 1ull);  // MPCB_DEBUG_TIMERS=2
+    if (s_desc.debug >= 2) atomicAdd(&g_dbg_calls[fast ? 0 : 1], 1ull);  // MPCB_DEBUG_TIMERS=2
     const double avx = fabs(vx);
     const bool wide = !fast && avx > 0x1p-960 && avx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX && v.trig_ok &&
                       fabs(a_f) < 0x1p1000 && fabs(a_r) < 0x1p1000;
     // The vote only picks which of two bit-identical routes the fast lanes take, so any set of voters is fine.
     const unsigned act = __activemask();
     const bool any_wide = __ballot_sync(act, wide) != 0u;
-    if (s_desc.debug >= 2 && s_desc.debug < 5) {
+    if (s_desc.debug >= 2) {
       const bool is_nan_d = !(q[0] == q[0] && vx == vx && q[2] == q[2] && q[3] == q[3]);
       const bool slow_d = !fast && !wide && !is_nan_d;
       if (!fast) atomicAdd(&g_dbg_calls[wide ? 2 : (is_nan_d ? 3 : 4)], 1ull);
@@ -586,10 +586,7 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
     const double ud = ud_next, udl = udl_next;
     if (n + 1 < d.N) { ud_next = U(2 * n + 2); udl_next = U(2 * n + 3); }
     const int o = n * K;
-    const bool prof = d.debug >= 5 && J == 0;  // MPCB_DEBUG_TIMERS=5: where a split evaluation's cycles go
-    const long long tp0 = prof ? clock64() : 0;
     stage_fm_split<MODEL>(y, ud, udl, scr, o, J);
-    const long long tp1 = prof ? clock64() : 0;
     bool sane = true;
 #pragma unroll
     for (int i = 0; i < NX; ++i) sane = sane && y[i] == y[i];
@@ -600,12 +597,6 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
     if (J == 0) {
 #pragma unroll
       for (int i = 0; i < NX; ++i) scr.set(o + NX * ND + 2 + i, gy[i]);
-    }
-    if (prof) {
-      const long long tp2 = clock64();
-      atomicAdd(&g_dbg_calls[0], (unsigned long long)(tp1 - tp0));
-      atomicAdd(&g_dbg_calls[1], (unsigned long long)(tp2 - tp1));
-      atomicAdd(&g_dbg_calls[5], 1ull);
     }
   }
   __syncwarp(gmask);  // the columns written by the other lanes of the group are visible to the leader
