@@ -161,6 +161,23 @@ int mpcb_value_grad(MpcHandle* h, int64_t B, const double* x0, const double* U, 
                     const double* lambda /*[B,nx*N] or NULL*/, const double* Sigma /*[B,nx*N] or NULL*/,
                     double* cost_out /*[B]*/, double* grad_out /*[B,2N]*/, void* stream);
 
+/* Allocation-free ψ and ∇_U ψ.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments, kernel and results as mpcb_value_grad; the stage-Jacobian scratch is a file-scope static
+ * device array of MPCB_STATIC_SCRATCH_BYTES (held by every GPU that loads the library until exit) instead of the
+ * handle's grow-only workspace, so the call makes no cudaMalloc / cudaFree and launches one kernel.
+ * Limits (rejected with MPCB_E_UNSUPPORTED and a message in mpcb_last_error): B <= MPCB_STATIC_MAX_B; road_mode
+ * MPCB_ROAD_SHARED or MPCB_ROAD_TABLE only (the per-instance and Bezier layouts need allocated scratch).  The
+ * handle's device must be the current device.  The array is shared by every call on the device and keeps the last
+ * call's contents (nothing in it needs to start at zero): calls that overlap on the GPU — two streams, two
+ * handles — race; serialise them. */
+#define MPCB_STATIC_SCRATCH_BYTES (32u << 20)
+#define MPCB_STATIC_MAX_B (1 << 20)
+int mpcb_value_grad_static(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p,
+                           const double* road, const int32_t* road_idx, const double* obs,
+                           const double* lambda /*[B,nx*N] or NULL*/, const double* Sigma /*[B,nx*N] or NULL*/,
+                           double* cost_out /*[B]*/, double* grad_out /*[B,2N]*/, void* stream);
+
 /* The MPC step's NLP solve: replaces `self.solver(problem, U, λ)` (controller.py:57).
  * U_inout / lambda_inout carry the warm start in and the solution out (controller.py:20-21,57). */
 int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double* x0, const double* p,

@@ -18,6 +18,7 @@ STATUS_UNKNOWN, STATUS_CONVERGED, STATUS_MAX_TIME, STATUS_MAX_ITER = 0, 1, 2, 3
 STATUS_NOT_FINITE, STATUS_NO_PROGRESS, STATUS_INTERRUPTED = 4, 5, 6
 E_ARG, E_CUDA, E_UNSUPPORTED, E_NODEVICE = -1, -2, -3, -4
 NP, OBS_DIM, MAX_N, MAX_OBS = 22, 5, 64, 8
+STATIC_SCRATCH_BYTES, STATIC_MAX_B = 32 << 20, 1 << 20  # mpcb_value_grad_static
 
 
 class MpcProblemDesc(C.Structure):
@@ -66,6 +67,7 @@ SIGNATURES = {
     "mpcb_bezier_sample": (C.c_int, [C.c_void_p, _I64, _P, _P, _P]),
     "mpcb_rollout": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "mpcb_value_grad": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "mpcb_value_grad_static": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "mpcb_solve": (C.c_int, [C.c_void_p, C.POINTER(MpcSolverParams), _I64] + [_P] * 15),
     "mpcb_solve_host": (C.c_int, [C.c_void_p, C.POINTER(MpcSolverParams), _I64] + [_P] * 14),
     "mpcb_last_transfer_bytes": (None, [C.c_void_p, C.POINTER(_I64), C.POINTER(_I64)]),

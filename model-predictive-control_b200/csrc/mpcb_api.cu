@@ -740,3 +740,87 @@ int mpcb_fp64_peak(double* tflops_out, double* ms_out) {
 }
 
 }  // extern "C"
+
+// ---- allocation-free psi + grad psi (no counterpart in the reference) ----
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+// Same kernel as mpcb_value_grad (k_value_grad), but its stage-Jacobian scratch [N * stage_doubles, lanes] lives in
+// a file-scope static device array instead of the handle's grow-only cudaMalloc'ed workspace.  Every GPU that loads
+// the library holds MPCB_STATIC_SCRATCH_BYTES until exit.  The array is shared by EVERY call on a device (all
+// handles, all streams) and keeps the last call's contents: nothing in it has to start at zero (a lane writes its
+// stage rows in the forward pass before its adjoint reads them back), but two calls that overlap on the GPU race.
+#include <mutex>
+
+namespace {
+constexpr size_t kStaticScratchDoubles = MPCB_STATIC_SCRATCH_BYTES / sizeof(double);
+static __device__ __align__(256) double g_static_scratch[kStaticScratchDoubles];
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: the device address is looked up
+// once per device (with that device current) and cached here.
+constexpr int kMaxDevices = 64;
+double* g_static_scratch_ptr[kMaxDevices] = {};
+std::mutex g_static_scratch_mu;
+
+int static_scratch_ptr(MpcHandle* h, double** out) {
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev != h->device) return fail(h, MPCB_E_ARG, "mpcb_value_grad_static: the handle's device is not the current device");
+  if (dev < 0 || dev >= kMaxDevices) return fail(h, MPCB_E_UNSUPPORTED, "mpcb_value_grad_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+  if (!g_static_scratch_ptr[dev]) {
+    double* ptr = nullptr;
+    CK(cudaGetSymbolAddress((void**)&ptr, g_static_scratch));
+    if (!ptr) return fail(h, MPCB_E_CUDA, "mpcb_value_grad_static: cudaGetSymbolAddress returned a null address");
+    g_static_scratch_ptr[dev] = ptr;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int mpcb_value_grad_static(MpcHandle* h, int64_t B, const double* x0, const double* U, const double* p,
+                           const double* road, const int32_t* road_idx, const double* obs, const double* lambda,
+                           const double* Sigma, double* cost_out, double* grad_out, void* stream) {
+  if (!h || B < 0) return fail(h, MPCB_E_ARG, "mpcb_value_grad_static: bad argument");
+  if (B == 0) return MPCB_OK;
+  if (!x0 || !U || !p || !road || !cost_out || !grad_out) return fail(h, MPCB_E_ARG, "mpcb_value_grad_static: null argument");
+  if (B > (int64_t)MPCB_STATIC_MAX_B)
+    return fail(h, MPCB_E_UNSUPPORTED, "mpcb_value_grad_static: B = " + std::to_string(B) + " exceeds MPCB_STATIC_MAX_B = " +
+                                           std::to_string((long long)MPCB_STATIC_MAX_B) + " (use mpcb_value_grad)");
+  const KDesc& k = h->kd;
+  if ((k.flags & MPCB_FLAG_OBST) && k.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  // per-instance and Bezier roads need a [2S, B] transposed copy in grow-only (cudaMalloc'ed) scratch
+  if (k.road_mode != MPCB_ROAD_SHARED && k.road_mode != MPCB_ROAD_TABLE)
+    return fail(h, MPCB_E_UNSUPPORTED, "mpcb_value_grad_static: only MPCB_ROAD_SHARED / MPCB_ROAD_TABLE roads (the other "
+                                       "layouts need allocated scratch; use mpcb_value_grad)");
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  double* scratch = nullptr;
+  if ((rc = static_scratch_ptr(h, &scratch))) return rc;
+  const int block = 128;
+  const size_t rows = (size_t)k.N * (k.model_id == MPCB_MODEL_PACEJKA6 ? fm_stage_doubles<MPCB_MODEL_PACEJKA6>()
+                                                                       : fm_stage_doubles<MPCB_MODEL_KINEMATIC4>());
+  int64_t blocks = (B + block - 1) / block;
+  const int64_t max_blocks = (int64_t)h->num_sms * 8;
+  const int64_t cap_blocks = (int64_t)(kStaticScratchDoubles / (rows * block));  // lanes the static scratch holds
+  if (cap_blocks < 1)
+    return fail(h, MPCB_E_UNSUPPORTED, "mpcb_value_grad_static: one CTA's stage rows (" + std::to_string(rows * block * 8) +
+                                           " bytes) exceed MPCB_STATIC_SCRATCH_BYTES");
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks > cap_blocks) blocks = cap_blocks;
+  const int64_t ns = blocks * block;
+  if ((rc = enter(h, st))) return rc;
+  RoadArg ra; size_t smem;
+  if ((rc = prepare_road(h, B, road, road_idx, st, &ra, &smem))) return rc;  // table modes: no launch, no allocation
+  if (k.model_id == MPCB_MODEL_PACEJKA6) {
+    if ((rc = set_smem(h, k_value_grad<MPCB_MODEL_PACEJKA6>, smem))) return rc;
+    k_value_grad<MPCB_MODEL_PACEJKA6><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, scratch, ns);
+  } else {
+    if ((rc = set_smem(h, k_value_grad<MPCB_MODEL_KINEMATIC4>, smem))) return rc;
+    k_value_grad<MPCB_MODEL_KINEMATIC4><<<(unsigned)blocks, block, smem, st>>>(k, B, x0, U, p, ra, obs, lambda, Sigma, cost_out, grad_out, scratch, ns);
+  }
+  h->launches++;
+  return leave(h, st);
+}
+
+}  // extern "C"

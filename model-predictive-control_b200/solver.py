@@ -198,6 +198,22 @@ class BatchedMpc:
                                              self._stream()), self._h, "mpcb_value_grad")
         return cost, grad
 
+    def value_grad_static(self, x0, U, road, cost, grad, road_idx=None, obs=None, lam=None, Sigma=None, p=None):
+        """mpcb_value_grad_static: psi and grad psi with NO allocation anywhere (static device scratch; see
+        include/mpcb200.h for the limits).  Every argument must already be a contiguous CUDA tensor of the right
+        dtype on this device — nothing is converted, copied or allocated here — and `cost` [B], `grad` [B, 2N]
+        are written in place."""
+        f64, i32 = torch.float64, torch.int32
+        p = self.p if p is None else p
+        B = x0.shape[0]
+        with torch.cuda.device(self.device):
+            _ffi.check(self._lib.mpcb_value_grad_static(
+                self._h, B, _dev_ptr(x0, f64, "x0"), _dev_ptr(U, f64, "U"), _dev_ptr(p, f64, "p"),
+                _dev_ptr(road, f64, "road"), _dev_ptr(road_idx, i32, "road_idx"), _dev_ptr(obs, f64, "obs"),
+                _dev_ptr(lam, f64, "lam"), _dev_ptr(Sigma, f64, "Sigma"), _dev_ptr(cost, f64, "cost"),
+                _dev_ptr(grad, f64, "grad"), self._stream()), self._h, "mpcb_value_grad_static")
+        return cost, grad
+
     def solve(self, x0, road, U, lam=None, road_idx=None, obs=None, lb=None, ub=None, sp=None, p=None):
         """The MPC step's NLP solve (controller.py:57).  U (and lam) are updated IN PLACE (warm start
         in, solution out) and also returned together with per-instance statistics."""
