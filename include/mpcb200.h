@@ -44,6 +44,9 @@ extern "C" {
 #define MPCB_FLAG_LANE 1      /* add u_trgl + u_rbd (dpf_test.py:45-54) to every stage */
 #define MPCB_FLAG_OBST 2      /* add dnf (dpf_test.py:81-102) for n_obs obstacles to every stage */
 #define MPCB_FLAG_BOUNDED_D 4 /* state constraints g (main.py:43-52) are bounded by D_lower/D_upper */
+#define MPCB_FLAG_EXACT 8     /* diagnostic: solver shortcuts off (early line-search rejection, descent-lemma steps
+                                 decided without psi(x̂+), evaluations cut at a blown-up state); same iterates, slower;
+                                 MPCB_EXACT=1 in the environment sets it for every handle */
 
 /* status: alpaqa 0.0.1 SolverStatus order (reference controller.py:64 compares against Converged) */
 #define MPCB_STATUS_UNKNOWN 0
@@ -195,6 +198,12 @@ int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const do
                     const double* lb, const double* ub, double* U_inout, double* lambda_inout,
                     int32_t* status_out, int32_t* iters_out, int32_t* evals_out, double* psi_out,
                     double* res_out);
+
+/* Final step size gamma of every instance's last PANOC run in the last mpcb_solve / mpcb_solve_host on this handle
+ * (the `final γ` of alpaqa's inner-solver statistics, which controller.py:59-61 prints a subset of): the scale of the
+ * stopping test ||x̂ - x||_2 <= eps, needed to re-check a returned U* as a fixed point of the forward-backward map.
+ * gamma_out is a DEVICE pointer [B]; B at most the last solve's batch. */
+int mpcb_last_final_gamma(MpcHandle* h, int64_t B, double* gamma_out, void* stream);
 
 /* Bytes moved by the last mpcb_solve_host call (bench.py's e2e.h2d/d2h_bytes_per_step). */
 void mpcb_last_transfer_bytes(MpcHandle* h, int64_t* h2d, int64_t* d2h);

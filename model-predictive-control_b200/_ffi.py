@@ -13,7 +13,7 @@ LIB_PATH = os.environ.get("MPCB_LIB") or os.path.join(_HERE, "libmpcb200.so")
 # model / road / flag constants (include/mpcb200.h)
 MODEL_PACEJKA6, MODEL_KINEMATIC4 = 0, 1
 ROAD_SHARED, ROAD_TABLE, ROAD_PER_INSTANCE, ROAD_BEZIER = 0, 1, 2, 3
-FLAG_LANE, FLAG_OBST, FLAG_BOUNDED_D = 1, 2, 4
+FLAG_LANE, FLAG_OBST, FLAG_BOUNDED_D, FLAG_EXACT = 1, 2, 4, 8
 STATUS_UNKNOWN, STATUS_CONVERGED, STATUS_MAX_TIME, STATUS_MAX_ITER = 0, 1, 2, 3
 STATUS_NOT_FINITE, STATUS_NO_PROGRESS, STATUS_INTERRUPTED = 4, 5, 6
 E_ARG, E_CUDA, E_UNSUPPORTED, E_NODEVICE = -1, -2, -3, -4
@@ -70,6 +70,7 @@ SIGNATURES = {
     "mpcb_value_grad_static": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "mpcb_solve": (C.c_int, [C.c_void_p, C.POINTER(MpcSolverParams), _I64] + [_P] * 15),
     "mpcb_solve_host": (C.c_int, [C.c_void_p, C.POINTER(MpcSolverParams), _I64] + [_P] * 14),
+    "mpcb_last_final_gamma": (C.c_int, [C.c_void_p, _I64, _P, _P]),
     "mpcb_last_transfer_bytes": (None, [C.c_void_p, C.POINTER(_I64), C.POINTER(_I64)]),
     "mpcb_plant_step": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P]),
     "mpcb_fp64_peak": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),

@@ -32,6 +32,10 @@ struct MpcHandle {
   int tile_override = 0;                               // MPCB_TILE env: force the lanes-per-instance width
   int last_tile = 0;
   int mode_override = -1;                              // MPCB_MODE env: 0 persistent kernel, 1 rounds
+  int spec_w = 0;                                      // MPCB_SPECW env: fixed speculation window (0 = device policy)
+  int spec_live_wide = 4096, spec_live_mid = 12288;    // MPCB_SPEC_LIVE="wide,mid": live-tile thresholds of the policy
+  int split_ok = 1;                                    // MPCB_SPLIT env (0: never use the split evaluation)
+  long long eval_trace_round = -1;                     // MPCB_EVAL_TRACE env
   int last_mode = 0;
   int64_t last_rounds = 0;
   double last_eval_ms = 0.0, last_trans_ms = 0.0;
@@ -46,6 +50,7 @@ struct MpcHandle {
   const char* round_log = nullptr;                     // MPCB_ROUND_LOG=path: per-round [grad requests, psi requests, T ms, E ms]
   unsigned long long* queue = nullptr;
   double* zero_lam = nullptr; size_t zero_lam_cap = 0;
+  double* gam = nullptr; size_t gam_cap = 0; int64_t gam_B = 0;  // final step sizes of the last solve
   // staging for *_host entry points
   void* pin = nullptr; size_t pin_cap = 0;
   void* dev = nullptr; size_t dev_cap = 0;
@@ -94,6 +99,7 @@ KDesc make_kdesc(const MpcProblemDesc& d) {
   k.obs_Af = d.obs_Af; k.obs_b = d.obs_b; k.obs_sx = d.obs_sigma_x; k.obs_sy = d.obs_sigma_y; k.obs_adiv = d.obs_alpha_div;
   k.bounded = 0;
   k.debug = 0;
+  k.exact = (d.flags & MPCB_FLAG_EXACT) ? 1 : 0;
   // psi = sum of c_i * (error)^2 + lane potentials + obstacle Gaussians + Sigma/2 dist^2 (mpcb_cost.cuh)
   k.psi_nonneg = 1;
   for (int i = 0; i < 6; ++i) if (!(d.c[i] >= 0.0)) k.psi_nonneg = 0;
@@ -227,15 +233,23 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
   }
   if (const char* e = std::getenv("MPCB_TILE")) {
     int g = std::atoi(e);
-    if (g == 1 || g == 2 || g == 4 || g == 8) h->tile_override = g;
+    if (g == 1 || g == 8) h->tile_override = g;
   }
+  if (const char* e = std::getenv("MPCB_EXACT")) { if (std::atoi(e) != 0) h->kd.exact = 1; }
+  if (const char* e = std::getenv("MPCB_SPECW")) { int w = std::atoi(e); if (w >= 1 && w <= 7) h->spec_w = w; }
+  if (const char* e = std::getenv("MPCB_SPEC_LIVE")) {
+    int a = 0, b = 0;
+    if (std::sscanf(e, "%d,%d", &a, &b) == 2 && a >= 0 && b >= a) { h->spec_live_wide = a; h->spec_live_mid = b; }
+  }
+  if (const char* e = std::getenv("MPCB_SPLIT")) h->split_ok = std::atoi(e) != 0;
+  if (const char* e = std::getenv("MPCB_EVAL_TRACE")) h->eval_trace_round = std::atoll(e);
   *out = h;
   return MPCB_OK;
 }
 
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
-  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->dev);
+  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->dev);
   cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_counters);
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
@@ -368,7 +382,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   if (B == 0) return MPCB_OK;
   if (!x0 || !p || !road || !lb || !ub || !U || !status || !iters || !evals || !psi || !res)
     return fail(h, MPCB_E_ARG, "mpcb_solve: null argument");
-  if (sp->lbfgs_mem < 1 || sp->lbfgs_mem > 2 * MPCB_MAX_N || sp->max_iter < 0) return fail(h, MPCB_E_ARG, "mpcb_solve: bad solver params");
+  if (sp->lbfgs_mem < 1 || sp->lbfgs_mem > 2 * MPCB_MAX_N || sp->max_iter < 0 || sp->max_no_progress < 1 || sp->alm_max_iter < 1)
+    return fail(h, MPCB_E_ARG, "mpcb_solve: bad solver params (lbfgs_mem in [1, 2 MPCB_MAX_N], max_iter >= 0, max_no_progress >= 1, alm_max_iter >= 1)");
   if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
   cudaStream_t st = (cudaStream_t)stream;
   const KDesc& k = h->kd;
@@ -399,10 +414,12 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     // is throughput-bound (about 4 requests per evaluating lane in flight)
     // measured (profiles/r01_round_mode.md): G = 8 wins at every batch size up to 65536 (fewest rounds; idle lanes are
     // free); narrower tiles only to keep the per-lane workspace of very large batches within ~8 GB
+    // (per-lane rows + the per-tile L-BFGS history; tile widths are 8 or 1)
     G = 8;
-    while (G > 1 && (double)B * G * (8.0 * k.n + (k.bounded ? k.N * k.nx : 0)) * 8.0 > 8e9) G >>= 1;
+    const double per_tile = 8.0 * ((double)G * (8.0 * k.n + (k.bounded ? k.N * k.nx : 0)) + 2.0 * sp->lbfgs_mem * k.n);
+    if ((double)B * per_tile > 24e9) G = 1;
   } else {
-    for (int g : {8, 4, 2}) if (B * g <= (int64_t)h->num_sms * 8 * 32) { G = g; break; }
+    if (B * 8 <= (int64_t)h->num_sms * 8 * 32) G = 8;
   }
   if (h->tile_override > 0) G = h->tile_override;
   // + box [2n] + the two-loop recursion scalars of the CTA's tiles [64 / G][2 mem]
@@ -422,12 +439,15 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   if ((rc = grow(h, &h->ws, &h->ws_cap, (size_t)LM.total * ns * sizeof(double), st))) return rc;
   if ((rc = grow(h, &h->wst, &h->wst_cap, (size_t)TM.total * nt * sizeof(double), st))) return rc;
   CK(cudaMemsetAsync(h->queue, 0, sizeof(unsigned long long), st));
+  if ((rc = grow(h, &h->gam, &h->gam_cap, (size_t)B * sizeof(double), st))) return rc;
+  h->gam_B = B;
   SolveArgs a;
   std::memset(&a, 0, sizeof(a));
   a.B = B; a.x0 = x0; a.p = p; a.obs = obs; a.lb = lb; a.ub = ub; a.ra = ra; a.U = U; a.lam = lambda;
-  a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res;
+  a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res; a.gam_out = h->gam;
   a.ws = h->ws; a.wst = h->wst; a.ns = ns; a.nt = nt; a.queue = h->queue;
   a.dbg = nullptr;
+  a.spec_w = h->spec_w; a.spec_live_wide = h->spec_live_wide; a.spec_live_mid = h->spec_live_mid; a.ctl = nullptr;
   h->kd.debug = h->debug_timers;
   h->last_tile = G;
   h->last_mode = mode;
@@ -443,10 +463,10 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     if ((rc = grow(h, (char**)&h->rs_req, &h->rs_req_cap, ns8 * (3 * 4 + 4 * 8) + 64, st))) return rc;
     if ((rc = grow(h, &h->rs_escr, &h->rs_escr_cap, (size_t)k.N * stage_doubles * ens * sizeof(double), st))) return rc;
     if (!h->rs_counters) {
-      CK(cudaMalloc((void**)&h->rs_counters, 8 * sizeof(unsigned)));
+      CK(cudaMalloc((void**)&h->rs_counters, 16 * sizeof(unsigned)));  // [2][4] round counters + [4] control words
       CK(cudaMallocHost((void**)&h->rs_counters_host, 64 * 4 * sizeof(unsigned)));
     }
-    CK(cudaMemsetAsync(h->rs_counters, 0, 8 * sizeof(unsigned), st));
+    CK(cudaMemsetAsync(h->rs_counters, 0, 16 * sizeof(unsigned), st));
     char* rq = (char*)h->rs_req;
     a.req_b = (int64_t*)rq;
     a.req_p = (double**)(rq + ns8 * 8);
@@ -455,15 +475,14 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     a.req_want = (int32_t*)(rq + ns8 * 32);
     a.list_grad = (int32_t*)(rq + ns8 * 36);
     a.list_val = (int32_t*)(rq + ns8 * 40);
-    a.sd = h->rs_d; a.si = h->rs_i; a.counters = h->rs_counters;
+    a.sd = h->rs_d; a.si = h->rs_i; a.counters = h->rs_counters; a.ctl = h->rs_counters + 8;
     EvalArgs e;
     std::memset(&e, 0, sizeof(e));
     e.ns = ns; e.nt = nt; e.ens = ens; e.G = G;
     e.x0 = x0; e.p = p; e.obs = obs; e.lam = lambda; e.sig_base = h->wst + (size_t)TM.SIG * nt; e.ra = ra;
     e.req_want = a.req_want; e.req_b = a.req_b; e.req_p = a.req_p; e.req_g = a.req_g; e.req_val = a.req_val;
-    e.list_grad = a.list_grad; e.list_val = a.list_val; e.escr = h->rs_escr;
-    e.split_ok = 1;
-    if (const char* sv = std::getenv("MPCB_SPLIT")) e.split_ok = std::atoi(sv) != 0;
+    e.list_grad = a.list_grad; e.list_val = a.list_val; e.escr = h->rs_escr; e.ctl = h->rs_counters + 8;
+    e.split_ok = h->split_ok;
 #define MPCB_LAUNCH_T(MODEL, GG)                                                               \
   do {                                                                                         \
     if (round == 0 && (rc = set_smem(h, k_solve<MODEL, GG, true>, box_smem))) return rc;       \
@@ -472,25 +491,28 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
 #define MPCB_LAUNCH_T_G(MODEL)                                                                 \
   switch (G) {                                                                                 \
     case 8: MPCB_LAUNCH_T(MODEL, 8); break;                                                    \
-    case 4: MPCB_LAUNCH_T(MODEL, 4); break;                                                    \
-    case 2: MPCB_LAUNCH_T(MODEL, 2); break;                                                    \
     default: MPCB_LAUNCH_T(MODEL, 1); break;                                                   \
   }
     if (k.model_id == MPCB_MODEL_PACEJKA6) { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_PACEJKA6>, road_smem))) return rc; }
     else { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_KINEMATIC4>, road_smem))) return rc; }
     int64_t round = 0;
-    const int64_t round_cap = 4000000;
+    // no instance can need more: <= ~40 rounds per PANOC iteration (9 trials x descent-lemma steps) over at most
+    // max_iter iterations per PANOC run and ~8 runs of the tolerance continuation; a guard against a hang, not a limit
+    const int64_t round_cap = std::min<int64_t>(4000000, 64 + (int64_t)40 * (sp->max_iter + 8) * 10);
     int chunk = 48;
     for (cudaEvent_t& ev : h->rs_ev) if (!ev) CK(cudaEventCreate(&ev));
     if (h->debug_timers >= 2) {
       unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       CK(cudaMemcpyToSymbolAsync(g_dbg_calls, z, sizeof(z), 0, cudaMemcpyHostToDevice, st));
     }
-    std::FILE* log = h->round_log ? std::fopen(h->round_log, "w") : nullptr;
+    struct LogFile {  // closed on every return path
+      std::FILE* f;
+      ~LogFile() { if (f) std::fclose(f); }
+    } log_guard{h->round_log ? std::fopen(h->round_log, "w") : nullptr};
+    std::FILE* log = log_guard.f;
     // MPCB_EVAL_TRACE=r: per-chunk cycle counts of evaluation launch r, printed to stderr (diagnostic)
-    long long trace_round = -1;
-    if (const char* tr = std::getenv("MPCB_EVAL_TRACE")) {
-      trace_round = std::atoll(tr);
+    const long long trace_round = h->eval_trace_round;
+    if (trace_round >= 0) {
       if ((rc = grow(h, &h->dbg, &h->dbg_cap, (size_t)(ns / 32 + 2) * 2 * sizeof(long long), st))) return rc;
       CK(cudaMemsetAsync(h->dbg, 0, (size_t)(ns / 32 + 2) * 2 * sizeof(long long), st));
     }
@@ -555,7 +577,6 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     }
 #undef MPCB_LAUNCH_T_G
 #undef MPCB_LAUNCH_T
-    if (log) std::fclose(log);
     if (h->debug_timers >= 2) {
       unsigned long long c[8];
       if (cudaMemcpyFromSymbol(c, g_dbg_calls, sizeof(c)) == cudaSuccess)
@@ -581,8 +602,6 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
 #define MPCB_LAUNCH_SOLVE_G(MODEL)                                                             \
   switch (G) {                                                                                 \
     case 8: MPCB_LAUNCH_SOLVE(MODEL, 8); break;                                                \
-    case 4: MPCB_LAUNCH_SOLVE(MODEL, 4); break;                                                \
-    case 2: MPCB_LAUNCH_SOLVE(MODEL, 2); break;                                                \
     default: MPCB_LAUNCH_SOLVE(MODEL, 1); break;                                               \
   }
   if (k.model_id == MPCB_MODEL_PACEJKA6) { MPCB_LAUNCH_SOLVE_G(MPCB_MODEL_PACEJKA6) }
@@ -687,6 +706,17 @@ int64_t mpcb_debug_timers(MpcHandle* h, long long* out, int64_t max_warps) {
     std::fprintf(stderr, "[mpcb debug] model calls: fast path %llu, general path %llu (%.2f%%)\n", c[0], c[1],
                  100.0 * (double)c[1] / (double)(c[0] + c[1] + 1));
   return nw;
+}
+
+int mpcb_last_final_gamma(MpcHandle* h, int64_t B, double* gamma_out, void* stream) {
+  if (!h || !gamma_out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_last_final_gamma: bad argument");
+  if (B > h->gam_B || !h->gam) return fail(h, MPCB_E_ARG, "mpcb_last_final_gamma: the last solve on this handle had fewer instances");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  if ((rc = enter(h, st))) return rc;
+  CK(cudaMemcpyAsync(gamma_out, h->gam, (size_t)B * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  return leave(h, st);
 }
 
 void mpcb_last_transfer_bytes(MpcHandle* h, int64_t* h2d, int64_t* d2h) {

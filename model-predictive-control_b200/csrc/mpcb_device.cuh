@@ -19,6 +19,9 @@ namespace mpcb {
 // Everything the kernels need from MpcProblemDesc, passed by value (constant bank).
 struct KDesc {
   int model_id, N, S, n_sub, nx, n, m, n_obs, flags, road_mode, n_roads, bounded, debug;
+  int exact;       // MPCB_EXACT / MPCB_FLAG_EXACT: the solver's shortcuts are off (early line-search rejection, lemma
+                   // steps decided without psi(x̂+), evaluations cut at a blown-up state) — for the tests that show
+                   // the iterates do not depend on them
   int psi_nonneg;  // every cost term is a non-negative weight times a square / a Gaussian: psi >= 0 everywhere
   double h, Ts, v_ref, c[6];
   double kin_acc, kin_mu;

@@ -591,7 +591,7 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
 #pragma unroll
     for (int i = 0; i < NX; ++i) sane = sane && y[i] == y[i];
     sane = sane && fabs(y[3]) < 1.3e154 && (MODEL == MPCB_MODEL_KINEMATIC4 || fabs(y[NX == 6 ? 4 : 3]) < 1.3e154);
-    if (!sane) { dead = true; continue; }
+    if (!sane && !d.exact) { dead = true; continue; }
     double gy[NX], gu[2];
     cost += stage_cost<MODEL, true, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
     if (J == 0) {

@@ -44,6 +44,7 @@ struct SolveArgs {
   double *U, *lam;
   int32_t *status, *iters, *evals;
   double *psi, *res;
+  double* gam_out;  // [B] final step size gamma of every instance's last PANOC run (alpaqa's inner stats: final γ)
   double* ws;    // per-lane rows   [LaneMap.total, ns]
   double* wst;   // per-tile data   [TileMap.total, nt] (tile-vector region first, plain rows after)
   int64_t ns, nt;
@@ -60,9 +61,14 @@ struct SolveArgs {
   double* req_val;           // [ns] psi written by the evaluation kernel
   int32_t* list_grad;        // compacted lanes whose request wants a gradient
   int32_t* list_val;         // compacted lanes whose request wants psi only
-  unsigned* counters;        // [2][4] by round parity: gradient requests, value requests, evaluation work counter
+  unsigned* counters;        // [2][4] by round parity: gradient requests, value requests, evaluation work counter, live tiles
+  // Speculation window (tau candidates evaluated per round, 1 .. G-1): spec_w > 0 fixes it (MPCB_SPECW); 0 = picked on
+  // the device from the number of tiles still solving (ctl[0], written by the previous round's evaluation launch).
+  int spec_w;
+  int spec_live_wide, spec_live_mid;  // live tiles up to which the window is G-1 wide / 3 wide (1 beyond)
+  const unsigned* ctl;       // [4] device control words: [0] live tiles of the previous round
 };
-constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 25;
+constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 26;
 
 enum SolveState {
   ST_IDLE = 0, ST_START_PANOC, ST_INIT_G1, ST_LIP_DONE, ST_XHAT_REQ, ST_XHAT_DONE, ST_ITER_TOP, ST_FD_DONE,
@@ -111,7 +117,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     if (__syncthreads_and((a.si[s0] & 1024) != 0)) {
       if (s0 == 0) {
         unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
-        nx[0] = 0u; nx[1] = 0u; nx[2] = 0u;
+        nx[0] = 0u; nx[1] = 0u; nx[2] = 0u; nx[3] = 0u;
       }
       return;
     }
@@ -149,6 +155,22 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     return x;
   };
   auto tbcast = [&](double x, int src) { return __shfl_sync(tmask, x, tbase + src); };
+  // Dot products over a tile-vector in ONE summation order for every tile width, so that the iterates do not
+  // depend on G: element e belongs to class e % 8, a class is summed in increasing e, and the 8 class sums are
+  // combined as ((c0 + c4) + (c2 + c6)) + ((c1 + c5) + (c3 + c7)) — the order of tsum's xor-4, xor-2, xor-1 steps
+  // for G = 8, where lane l owns exactly class l.  A lane of a narrower tile owns CL = 8 / G classes (element
+  // e = l + G j is class l + G (j % CL)) and folds them locally before the shuffles.
+  constexpr int CL = G >= 8 ? 1 : 8 / G;
+  auto tsum_c = [&](const double* pc) {
+    double x;
+    if (CL == 1) x = pc[0];
+    else if (CL == 2) x = pc[0] + pc[1];
+    else if (CL == 4) x = (pc[0] + pc[2]) + (pc[1] + pc[3]);
+    else x = ((pc[0] + pc[4 % CL]) + (pc[2 % CL] + pc[6 % CL])) + ((pc[1 % CL] + pc[5 % CL]) + (pc[3 % CL] + pc[7 % CL]));
+#pragma unroll
+    for (int o = (G >= 8 ? 4 : G / 2); o > 0; o >>= 1) x += __shfl_xor_sync(tmask, x, o);
+    return x;
+  };
 
   // ---- tile-uniform registers ----
   int state = ST_IDLE;
@@ -159,6 +181,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   bool fd_ready = false;                 // the next iteration's FD gradient is already in lane fd_lane's P row of bank cb
   int fd_lane = 0, ge_row = 0, ge_lane = 0;
   int k = 0, no_prog = 0, lb_idx = 0, lb_full = 0, hb = 0, lsw = 0;
+  int lsW = G >= 2 ? G - 1 : 1;          // tau candidates per window of the running line search (1 .. G-1)
   unsigned specmask = 0;                 // candidates (by lane) whose FD speculation has been handed out
   double psi = 0, psi_hat = 0, gTp = 0, pTp = 0, L = 0, gam = 0, phi = 0, tau0 = 0, sigma = 0, hfd = 0, hh = 0;
   double eps_tol = 0, peps = 0, ppsi = 0, norm_e2 = 0;
@@ -178,7 +201,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
 #define MPCB_STATE_D(X) X(psi) X(psi_hat) X(gTp) X(pTp) X(L) X(gam) X(phi) X(tau0) X(sigma) X(hfd) X(hh) X(eps_tol) X(peps) \
   X(ppsi) X(norm_e2) X(psi_n) X(psi_hat_n) X(gTp_n) X(pTp_n) X(L_n) X(gam_n) X(phi_n)
 #define MPCB_STATE_I(X) X(state) X(cl) X(cb) X(fd_lane) X(ge_row) X(ge_lane) X(k) X(no_prog) X(lb_idx) X(lb_full) X(hb) X(lsw) \
-  X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for)
+  X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for) X(lsW)
   bool dead = false;  // round mode: this tile has no instance left
   if constexpr (ROUND) {
     if (a.round > 0) {
@@ -324,15 +347,20 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     for (int kk = 0; kk < cnt; ++kk) {
       int i = lb_idx - 1 - kk;
       if (i < 0) i += mem;
-      double sy = 0.0, yy = 0.0, sq = 0.0;
-      for (int j = 0; j < ne; ++j) {
-        int e = l + G * j;
-        if (e < n && mbit(e)) {
-          double s = tv(T.LS + i * T.np, e), y = tv(T.LY + i * T.np, e);
-          sy += s * y; yy += y * y; sq += s * tv(T.Q, e);
+      double syc[CL], yyc[CL], sqc[CL];
+#pragma unroll
+      for (int t = 0; t < CL; ++t) { syc[t] = 0.0; yyc[t] = 0.0; sqc[t] = 0.0; }
+      for (int j0 = 0; j0 < ne; j0 += CL) {
+#pragma unroll
+        for (int t = 0; t < CL; ++t) {
+          const int e = l + G * (j0 + t);
+          if (j0 + t < ne && e < n && mbit(e)) {
+            double s = tv(T.LS + i * T.np, e), y = tv(T.LY + i * T.np, e);
+            syc[t] += s * y; yyc[t] += y * y; sqc[t] += s * tv(T.Q, e);
+          }
         }
       }
-      sy = tsum(sy); yy = tsum(yy); sq = tsum(sq);
+      const double sy = tsum_c(syc), yy = tsum_c(yyc), sq = tsum_c(sqc);
       if (!(sy > 0.0)) { s_ra[i] = nan(""); continue; }
       double rho = 1.0 / sy;
       s_ra[i] = rho;
@@ -354,12 +382,17 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       if (i < 0) i += mem;
       double rho = s_ra[i];
       if (isnan(rho)) continue;
-      double yq = 0.0;
-      for (int j = 0; j < ne; ++j) {
-        int e = l + G * j;
-        if (e < n && mbit(e)) yq += tv(T.LY + i * T.np, e) * tv(T.Q, e);
+      double yqc[CL];
+#pragma unroll
+      for (int t = 0; t < CL; ++t) yqc[t] = 0.0;
+      for (int j0 = 0; j0 < ne; j0 += CL) {
+#pragma unroll
+        for (int t = 0; t < CL; ++t) {
+          const int e = l + G * (j0 + t);
+          if (j0 + t < ne && e < n && mbit(e)) yqc[t] += tv(T.LY + i * T.np, e) * tv(T.Q, e);
+        }
       }
-      yq = tsum(yq);
+      const double yq = tsum_c(yqc);
       double coef = s_ra[mem + i] - rho * yq;
       for (int j = 0; j < ne; ++j) {
         int e = l + G * j;
@@ -369,22 +402,28 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   };
 
   // Line-search candidates (Appendix A 3d): c = 0..7 -> tau = 2^-c, c = 8 -> the prox step x̂ (forced
-  // accept).  Lane order is trial order: the last lane of the tile holds c = 8 from the start (long runs of
-  // iterations in which every tau fails are what the slowest instances of a batch are made of), the
-  // lanes below it hold a window of G-1 consecutive tau candidates, right-aligned, that slides when all
-  // of its candidates are rejected.  G = 1: one candidate at a time, c = lsw.  tau0 = 0 (k = 0 or a
-  // non-finite q): only the prox step.  Newly assigned candidates request psi and grad psi.
-  auto ls_assign = [&](bool first) {
+  // accept).  Lane order is trial order: the last lane of the tile holds c = 8, the lanes below it hold a
+  // window of lsW consecutive tau candidates (1 <= lsW <= G-1), right-aligned, that slides when all of its
+  // candidates are rejected.  The window width is the amount of SPECULATION, never a decision: candidates are
+  // decided in trial order whatever the width, so every width gives the same iterates (tests: W = 1 vs W = 7
+  // bit-identical).  Wide (lsW = G-1, picked when the GPU has lanes to spare): all trials of Appendix A 3d in two
+  // windows and the prox step evaluated from the start (long runs of iterations in which every tau fails are what
+  // the slowest instances of a batch are made of).  Narrow (lsW = 1, the bulk of a large batch, where every
+  // evaluation costs throughput): one trial at a time like sequential back-tracking, the prox step only once every
+  // tau has failed (`fb_now`).  G = 1: one candidate at a time, c = lsw.  tau0 = 0 (k = 0 or a non-finite q):
+  // only the prox step.  Newly assigned candidates request psi and grad psi.
+  auto ls_assign = [&](bool first, bool fb_now) {
     const int nb = cb ^ 1;
     bool mine = false, valid = false;
     if (G == 1) {
       c_idx = tau0 == 0.0 ? 8 : lsw;
       mine = true; valid = true;
     } else if (l == G - 1) {
-      if (first) { c_idx = 8; mine = true; valid = true; }
-    } else {
-      const int c_first = lsw * (G - 1);
-      const int cnt = 8 - c_first < G - 1 ? 8 - c_first : G - 1;
+      if (fb_now || (first && (lsW == G - 1 || tau0 == 0.0))) { c_idx = 8; mine = true; valid = true; }
+      else if (first) { c_idx = 8; mine = true; valid = false; }  // narrow window: handed out later (fb_now)
+    } else if (!fb_now) {
+      const int c_first = lsw * lsW;
+      const int cnt = 8 - c_first < lsW ? 8 - c_first : lsW;
       const int j = l - (G - 1 - cnt);
       c_idx = c_first + j;
       mine = true; valid = tau0 != 0.0 && j >= 0;
@@ -439,6 +478,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       // re-evaluations at x+ + 1e12 window slides
       a.psi[b] = d.debug >= 3 ? (double)t_rounds + 1e4 * dbg_fd + 1e8 * dbg_lemma + 1e12 * dbg_slide : ppsi;
       a.res[b] = peps;
+      if (a.gam_out) a.gam_out[b] = gam;
     }
     n_val = 0; n_grad = 0; t_rounds = 0; dbg_fd = 0; dbg_lemma = 0; dbg_slide = 0;
   };
@@ -618,7 +658,18 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         sigma = (1.0 - gam * L) * pTp / (2.0 * gam);
         lsw = 0; specmask = 0;
         fd_done = false; spec_for = -1;
-        ls_assign(true);
+        // speculation width of this line search (constant until its end)
+        if (G >= 2) {
+          int w = a.spec_w;
+          if (w <= 0) {
+            // device policy: a tile in a wide window costs ~8 evaluations per round; while more tiles are solving
+            // than the evaluation launch has lanes for, every one of them costs throughput, so trials go one at a time
+            const unsigned live = a.ctl ? a.ctl[0] : 0u;
+            w = live <= (unsigned)a.spec_live_wide ? G - 1 : (live <= (unsigned)a.spec_live_mid ? 3 : 1);
+          }
+          lsW = w > G - 1 ? G - 1 : w;
+        }
+        ls_assign(true, false);
         state = ST_LS_STEP;
         break;
       } else if (state == ST_LS_STEP) {
@@ -632,6 +683,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         // guard covers the rounding of the two gamma-dependent terms (40-term dot products) and of the
         // two additions; inside it the candidate is evaluated in full.  NaN fails (as in the sequential test).
         auto ls_hopeless = [&]() {
+          if (d.exact) return false;
           const double s2 = pTp_n / (2.0 * gam_n);
           const double lc = psi_n + s2 + gTp_n - (phi - sigma);
           const double guard = 8.9e-16 * (1.0 + fabs(phi) + fabs(psi_n)) + 1e-12 * (fabs(gTp_n) + s2);
@@ -647,7 +699,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           for (;;) {
             if (!c_fb && ls_hopeless()) { c_pend = false; c_acc = false; return; }
             const double margin = (1.0 + fabs(psi_n)) * sp.quad_tol;
-            if (!(d.psi_nonneg && 0.0 - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max)) return;
+            if (d.exact || !(d.psi_nonneg && 0.0 - psi_n > gTp_n + 0.5 * L_n * pTp_n + margin && L_n * 2.0 <= sp.L_max)) return;
             L_n *= 2.0; gam_n *= 0.5;
             prox(WL(M.X(nb), l), WL(M.G(nb), l), gam_n, WL(M.XH(nb), l), WL(M.P(nb), l), gTp_n, pTp_n);
           }
@@ -684,15 +736,23 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         // the window of tau candidates slides once all of its lanes are rejected (the prox step on the last
         // lane cannot be accepted before every tau has been tried)
         const unsigned wmask = (1u << (G - 1)) - 1u;
-        const bool slide = G >= 2 && !((pm | am) & wmask) && tau0 != 0.0 && (lsw + 1) * (G - 1) <= 7;
+        const bool wdead = G >= 2 && !((pm | am) & wmask);  // every tau candidate of the window has been rejected
+        const bool slide = wdead && tau0 != 0.0 && (lsw + 1) * lsW <= 7;
+        // narrow windows hand out the prox-step candidate only now, when no tau is left to try
+        const bool fb_live = G >= 2 && ((__ballot_sync(tmask, c_valid && c_fb) & tmask) != 0u);
+        const bool need_fb = wdead && !slide && !fb_live;
         if (pm & below || first_acc == G || slide) {
           // earlier candidates are undecided (or, G = 1, the only candidate was rejected): another round
           if (G == 1) {
-            if (!c_pend) { ++lsw; ls_assign(false); }
+            if (!c_pend) { ++lsw; ls_assign(false, false); }
           } else {
+            if (need_fb) {
+              ls_assign(false, true);
+              pm = (__ballot_sync(tmask, c_valid && c_pend) & tmask) >> tbase;
+            }
             if (slide) {
               ++lsw; ++dbg_slide;
-              ls_assign(false);
+              ls_assign(false, false);
               // speculations made for the window's previous candidates are void
               if (spec_for >= 0 && spec_for < G - 1) { fd_done = false; spec_for = -1; }
               specmask &= ~wmask;
@@ -772,24 +832,36 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         const int jw = first_acc;
         {
           Vec X = WL(M.X(cb), cl), XN = WL(M.X(nb), jw), Gc = WL(M.G(cb), cl), GN = WL(M.G(nb), jw);
-          double sy = 0.0, ss = 0.0;
+          // The pair enters the history only if it is accepted (Appendix A 3e; alpaqa stores accepted pairs only):
+          // with a full buffer slot lb_idx holds the OLDEST live pair, which a rejected one must not destroy.
+          double syc[CL], ssc[CL];
+#pragma unroll
+          for (int t = 0; t < CL; ++t) { syc[t] = 0.0; ssc[t] = 0.0; }
           bool same = true;
-          for (int j = 0; j < ne; ++j) {
-            int e = l + G * j;
-            if (e < n) {
-              double xi = X(e), xni = XN(e);
-              double s = xni - xi, y = GN(e) - Gc(e);
-              tv(T.LS + lb_idx * T.np, e) = s;
-              tv(T.LY + lb_idx * T.np, e) = y;
-              sy += s * y;
-              ss += s * s;
-              same = same && (xi == xni);
+          for (int j0 = 0; j0 < ne; j0 += CL) {
+#pragma unroll
+            for (int t = 0; t < CL; ++t) {
+              const int e = l + G * (j0 + t);
+              if (j0 + t < ne && e < n) {
+                double xi = X(e), xni = XN(e);
+                double s = xni - xi, y = GN(e) - Gc(e);
+                syc[t] += s * y;
+                ssc[t] += s * s;
+                same = same && (xi == xni);
+              }
             }
           }
-          sy = tsum(sy); ss = tsum(ss);
+          const double sy = tsum_c(syc), ss = tsum_c(ssc);
           same = (__ballot_sync(tmask, !same) & tmask) == 0;
           const double tiny = 1.4916681462400413e-154;  // sqrt(DBL_MIN)
           if (isfinite(sy) && ss >= tiny && sy >= tiny) {
+            for (int j = 0; j < ne; ++j) {
+              const int e = l + G * j;
+              if (e < n) {
+                tv(T.LS + lb_idx * T.np, e) = XN(e) - X(e);
+                tv(T.LY + lb_idx * T.np, e) = GN(e) - Gc(e);
+              }
+            }
             if (++lb_idx == mem) { lb_idx = 0; lb_full = 1; }
           }
           if (no_prog > 0 || k % sp.max_no_progress == 0) no_prog = same ? no_prog + 1 : 0;
@@ -894,7 +966,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       unsigned* cnt = a.counters + 4 * (a.round & 1);
       if (slot == 0) {  // the other parity's counters: last read by the previous evaluation launch
         unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
-        nx[0] = 0u; nx[1] = 0u; nx[2] = 0u;
+        nx[0] = 0u; nx[1] = 0u; nx[2] = 0u; nx[3] = 0u;
       }
       if (!dead) {
         if (__ballot_sync(tmask, want != 0) & tmask) ++t_rounds;
@@ -902,10 +974,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       }
       const unsigned mg = __ballot_sync(0xffffffffu, want == 2);
       const unsigned mv = __ballot_sync(0xffffffffu, want == 1 || want == 3);
+      const unsigned ml = __ballot_sync(0xffffffffu, l == 0 && !dead);  // tiles still solving (speculation policy)
       unsigned bg = 0, bv = 0;
       if (lane == 0) {
         if (mg) bg = atomicAdd(&cnt[0], (unsigned)__popc(mg));
         if (mv) bv = atomicAdd(&cnt[1], (unsigned)__popc(mv));
+        if (ml) atomicAdd(&cnt[3], (unsigned)__popc(ml));
       }
       bg = __shfl_sync(0xffffffffu, bg, 0);
       bv = __shfl_sync(0xffffffffu, bv, 0);
@@ -950,8 +1024,11 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       for (int i = 0; i < NX; ++i) y0[i] = a.x0[b * NX + i];
       const Vec scr = WL(M.SCR, l);
       const Vec stv = want == 3 ? WL(M.ST, l) : Vec{nullptr, 0};
-      if (anyg) val = eval_fm<MODEL, true>(r, ex, y0, evp, scr, evg, want == 2, stv, IVec{nullptr, 0}, true);
-      else val = eval_fm<MODEL, false>(r, ex, y0, evp, scr, evg, false, stv, IVec{nullptr, 0}, true);
+      // ONE variant for every request of the persistent kernel (psi-only requests skip the stores): the bits of a
+      // psi must not depend on which other requests happen to share its warp in this trip.  (Until round 2 a psi-only
+      // request took the cheaper value-only variant when its whole warp was psi-only; the sin kernels of the two
+      // variants differ in the last bits, so results depended on co-scheduling: tests/test_gpu_exactness.py.)
+      val = eval_fm<MODEL, true>(r, ex, y0, evp, scr, evg, want == 2, stv, IVec{nullptr, 0}, !d.exact);
       if (want == 2) ++n_grad;
       else if (want == 1) ++n_val;
     }
@@ -984,6 +1061,7 @@ struct EvalArgs {
   double* req_val;
   const int32_t *list_grad, *list_val;
   unsigned* counters;       // this round's [4]
+  unsigned* ctl;            // [4] control words read by the next transition launch: [0] live tiles
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
   long long* trace;         // diagnostic (MPCB_EVAL_TRACE=round): per chunk [cycles, first slot] or null
   int split_ok;             // 0: never use the split evaluation (MPCB_SPLIT=0)
@@ -1008,6 +1086,7 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const int64_t eslot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const Vec scr{e.escr + eslot, e.ens};
   const unsigned ng = e.counters[0], nv = e.counters[1];
+  if (blockIdx.x == 0 && threadIdx.x == 0 && e.ctl) e.ctl[0] = e.counters[3];
   const unsigned n_warps = gridDim.x * (blockDim.x >> 5);
   const unsigned cv = (nv + 31u) >> 5;
   // few gradient requests (every chunk still gets a warp slot of its own on half the sub-partitions): 8 lanes per
@@ -1063,9 +1142,9 @@ k_eval_requests(KDesc d, EvalArgs e) {
       const Vec pt{e.req_p[slot], e.ns};
       const Vec out{e.req_g[slot], e.ns};
       double v;
-      if (grad) v = eval_fm<MODEL, true>(r, ex, y0, pt, scr, out, true, Vec{nullptr, 0}, IVec{nullptr, 0}, true);
+      if (grad) v = eval_fm<MODEL, true>(r, ex, y0, pt, scr, out, true, Vec{nullptr, 0}, IVec{nullptr, 0}, !d.exact);
       else v = eval_fm<MODEL, false>(r, ex, y0, pt, scr, Vec{nullptr, 0}, false, want == 3 ? out : Vec{nullptr, 0},
-                                     IVec{nullptr, 0}, true);
+                                     IVec{nullptr, 0}, !d.exact);
       e.req_val[slot] = v;
       nonfinite = !(fabs(v) < 1e300);
     }

@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _ffi
-from ._ffi import (FLAG_BOUNDED_D, FLAG_LANE, FLAG_OBST, MODEL_KINEMATIC4, MODEL_PACEJKA6, ROAD_BEZIER,
+from ._ffi import (FLAG_BOUNDED_D, FLAG_EXACT, FLAG_LANE, FLAG_OBST, MODEL_KINEMATIC4, MODEL_PACEJKA6, ROAD_BEZIER,
                    ROAD_PER_INSTANCE, ROAD_SHARED, ROAD_TABLE)
 
 
@@ -272,6 +272,14 @@ class BatchedMpc:
                                                  hp(obs), hp(lb), hp(ub), hp(U), hp(lam), hp(status), hp(iters),
                                                  hp(evals), hp(psi), hp(res)), self._h, "mpcb_solve_host")
         return U, lam, SolveStats(status, iters[:, 0], iters[:, 1], evals[:, 0], evals[:, 1], psi, res)
+
+    def last_final_gamma(self, B):
+        """[B] final PANOC step sizes of the last solve on this handle (alpaqa's inner stats `final γ`)."""
+        out = torch.empty(B, dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _ffi.check(self._lib.mpcb_last_final_gamma(self._h, B, _dev_ptr(out, torch.float64, "gamma"), self._stream()),
+                       self._h, "mpcb_last_final_gamma")
+        return out
 
     def last_transfer_bytes(self):
         a, b = C.c_int64(), C.c_int64()

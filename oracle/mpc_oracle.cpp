@@ -175,6 +175,34 @@ void orc_value_grad_batch(const MpcProblemDesc* d, int64_t B, const double* x0, 
   }
 }
 
+// Fixed-point residual of the forward-backward map at a GIVEN step size (Appendix A 2, 3b):
+//   r = || Pi_C(U - gamma grad psi(U)) - U ||_2,  psi_out = psi(U)      (unbounded D: psi = f).
+// The certificate tests/test_gpu_exactness.py issues for every GPU answer, with the GPU's own final gamma.
+void orc_fb_residual_batch(const MpcProblemDesc* d, int64_t B, const double* x0, const double* U, const double* p,
+                           const double* road, const int32_t* road_idx, const double* obs, const double* lb,
+                           const double* ub, const double* gamma, double* res_out, double* psi_out) {
+  const int nx = nx_of(d->model_id), N = d->N, n = 2 * N;
+#pragma omp parallel
+  {
+    std::vector<double> tmp, g(n);
+#pragma omp for schedule(static)
+    for (int64_t b = 0; b < B; ++b) {
+      const double* r = road_of(d, road, road_idx, b, tmp);
+      Instance<double> I = make_instance<double>(d, p, r, obs ? obs + b * d->n_obs * MPCB_OBS_DIM : nullptr, nullptr, nullptr);
+      const double* u = U + b * n;
+      const double psi = value_grad(I, x0 + b * nx, u, g.data());
+      double s = 0;
+      for (int i = 0; i < n; ++i) {
+        double v = u[i] - gamma[b] * g[i];
+        v = v < lb[i] ? lb[i] : (v > ub[i] ? ub[i] : v);
+        s += (v - u[i]) * (v - u[i]);
+      }
+      res_out[b] = std::sqrt(s);
+      if (psi_out) psi_out[b] = psi;
+    }
+  }
+}
+
 // threads <= 0: all cores.  Per-instance wall time (seconds) optionally written to time_out[B].
 void orc_solve_batch(const MpcProblemDesc* d, const MpcSolverParams* sp, int64_t B, const double* x0,
                      const double* p, const double* road, const int32_t* road_idx, const double* obs,

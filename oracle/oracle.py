@@ -26,27 +26,52 @@ _PD = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
 _PI = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
 
 
+FAST_LIB_PATH = os.path.join(_HERE, "libmpc_oracle_fast.so")
+
+
 def build(force=False):
-    if force or not os.path.exists(LIB_PATH):
+    if force or not os.path.exists(LIB_PATH) or not os.path.exists(FAST_LIB_PATH):
         subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
     return LIB_PATH
+
+
+def _bind(L):
+    L.orc_wrap_to_pi.restype = _D
+    L.orc_wrap_to_pi.argtypes = [_D]
+    L.orc_u_trgl.restype = _D
+    L.orc_u_trgl.argtypes = [_D, _D, _D]
+    L.orc_u_rbd.restype = _D
+    L.orc_u_rbd.argtypes = [_D, _D, _D, _D]
+    L.orc_dnf.restype = _D
+    L.orc_event_state.restype = _D
+    L.orc_event_state.argtypes = [_D] * 5
+    L.orc_num_threads.restype = C.c_int
+    return L
+
+
+class variant:
+    """`with oracle.variant("fast"):` — route every call of this module through the second build of the same sources
+    (oracle/Makefile: -O3, AVX2, fused multiply-adds).  Used only for the oracle-vs-oracle sensitivity yardstick."""
+
+    def __init__(self, name):
+        assert name == "fast"
+
+    def __enter__(self):
+        global _lib
+        build()
+        self._saved = lib()
+        _lib = _bind(C.CDLL(FAST_LIB_PATH))
+
+    def __exit__(self, *exc):
+        global _lib
+        _lib = self._saved
 
 
 def lib():
     global _lib
     if _lib is None:
         build()
-        L = C.CDLL(LIB_PATH)
-        L.orc_wrap_to_pi.restype = _D
-        L.orc_wrap_to_pi.argtypes = [_D]
-        L.orc_u_trgl.restype = _D
-        L.orc_u_trgl.argtypes = [_D, _D, _D]
-        L.orc_u_rbd.restype = _D
-        L.orc_u_rbd.argtypes = [_D, _D, _D, _D]
-        L.orc_dnf.restype = _D
-        L.orc_event_state.restype = _D
-        L.orc_event_state.argtypes = [_D] * 5
-        L.orc_num_threads.restype = C.c_int
+        L = _bind(C.CDLL(LIB_PATH))
         _lib = L
     return _lib
 
@@ -194,6 +219,23 @@ def solve(desc, sp, x0, road, U, lam=None, p=DEFAULT_P, road_idx=None, obs=None,
     if want_times:
         out["times"] = times
     return out
+
+
+def fb_residual(desc, x0, U, road, gamma, p=DEFAULT_P, road_idx=None, obs=None, lb=None, ub=None):
+    """(r [B], psi [B]): r = ||Pi_C(U - gamma grad psi(U)) - U||_2 with the oracle's gradient, psi = psi(U)."""
+    nx = 4 if desc.model_id == 1 else 6
+    x0 = f64(x0).reshape(-1, nx)
+    B, N = x0.shape[0], desc.N
+    U, road, p, gamma = f64(U).reshape(B, 2 * N), f64(road), f64(p), f64(gamma).reshape(B)
+    obs = None if obs is None else f64(obs)
+    if lb is None:
+        lb = np.tile([-p[10], -p[9]], N)
+        ub = -lb
+    lb, ub = f64(lb), f64(ub)
+    res, psi = np.zeros(B), np.zeros(B)
+    lib().orc_fb_residual_batch(C.byref(desc), C.c_int64(B), _p(x0), _p(U), _p(p), _p(road), _p(_i32(road_idx)), _p(obs),
+                                _p(lb), _p(ub), _p(gamma), _p(res), _p(psi))
+    return res, psi
 
 
 def count_ops(desc, x0, U, road, p=DEFAULT_P, obs=None):

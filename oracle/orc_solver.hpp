@@ -62,17 +62,22 @@ struct LBFGS {
   void reset() { idx = 0; full = false; }
   int count() const { return full ? mem : idx; }
   bool update(const double* x, const double* xn, const double* g, const double* gn) {
+    // The pair is stored only if it is accepted (Appendix A 3e): with a full buffer slot idx holds the oldest live
+    // pair, which a rejected pair must not destroy.
+    double sy = 0, ss = 0;
+    for (int i = 0; i < n; ++i) {
+      const double si = xn[i] - x[i], yi = gn[i] - g[i];
+      sy += si * yi;
+      ss += si * si;
+    }
+    const double tiny = std::sqrt(DBL_MIN);
+    if (!std::isfinite(sy) || !(ss >= tiny) || !(sy >= tiny)) return false;
     double* s = &S[size_t(idx) * n];
     double* y = &Y[size_t(idx) * n];
-    double sy = 0, ss = 0;
     for (int i = 0; i < n; ++i) {
       s[i] = xn[i] - x[i];
       y[i] = gn[i] - g[i];
-      sy += s[i] * y[i];
-      ss += s[i] * s[i];
     }
-    const double tiny = std::sqrt(DBL_MIN);
-    if (!std::isfinite(sy) || !(ss >= tiny) || !(sy >= tiny)) return false;  // pair rejected (slot reused)
     idx++;
     if (idx == mem) { idx = 0; full = true; }
     return true;
@@ -261,7 +266,7 @@ inline PanocResult panoc(Problem& P, const MpcSolverParams& sp, double* x, doubl
     } while (!(ls_cond <= (1 + std::fabs(phi)) * sp.ls_tol) && tau >= sp.tau_min);
     // L-BFGS update (Appendix A 3e) and no-progress counter
     lb.update(x, xn.data(), g.data(), gn.data());
-    if (no_progress > 0 || k % sp.max_no_progress == 0) {
+    if (no_progress > 0 || k % (sp.max_no_progress > 0 ? sp.max_no_progress : 1) == 0) {
       bool same = true;
       for (int i = 0; i < n; ++i) same = same && (x[i] == xn[i]);
       no_progress = same ? no_progress + 1 : 0;

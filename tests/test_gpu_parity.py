@@ -256,7 +256,7 @@ def test_solve_iteration_counts_track_oracle(mp, orc):
     assert abs(np.median(gi) - np.median(r["inner"])) <= 3
 
 
-@pytest.mark.parametrize("G", [8, 4, 2, 1])
+@pytest.mark.parametrize("G", [8, 1])
 def test_every_tile_width_tracks_oracle(mp, orc, G, monkeypatch):
     """The tile width (lanes per instance; picked from the batch size, forced here with MPCB_TILE) only changes
     how much of the line search is speculated, never its decisions: every width must take the oracle's
@@ -277,7 +277,7 @@ def test_every_tile_width_tracks_oracle(mp, orc, G, monkeypatch):
     assert abs(gi.mean() - r["inner"].mean()) < 0.03 * r["inner"].mean()
 
 
-@pytest.mark.parametrize("G", [8, 2, 1])
+@pytest.mark.parametrize("G", [8, 1])
 @pytest.mark.parametrize("bounded", [False, True])
 def test_round_mode_equals_persistent_mode(mp, G, bounded, monkeypatch):
     """The two execution modes of mpcb_solve (one persistent kernel / transition + evaluation launches per

@@ -1,5 +1,5 @@
 """Solve throughput by execution mode, tile width and batch size (run on the GPU box).
-PROBE="mode:G:B,..." e.g. "rounds:8:4096,persistent:8:4096".  One subprocess-free pass: the env overrides are
+PROBE="mode:G:B[:W],..." e.g. "rounds:8:4096,persistent:8:4096,rounds:8:65536:1" (W = MPCB_SPECW).  One subprocess-free pass: the env overrides are
 read at mpcb_create, so every combination gets its own handle."""
 import json
 import os
@@ -17,8 +17,13 @@ def main():
     combos = os.environ.get("PROBE", "rounds:8:4096,persistent:8:4096").split(",")
     rows = []
     for c in combos:
-        mode, G, B = c.split(":")
-        B = int(B)
+        f = c.split(":")
+        mode, G, B = f[0], f[1], int(f[2])
+        W = f[3] if len(f) > 3 else "0"   # speculation window: 0 = device policy, 1..7 fixed (MPCB_SPECW)
+        if W != "0":
+            os.environ["MPCB_SPECW"] = W
+        else:
+            os.environ.pop("MPCB_SPECW", None)
         os.environ["MPCB_MODE"] = mode
         if int(G) > 0:
             os.environ["MPCB_TILE"] = G
@@ -41,7 +46,7 @@ def main():
             if i > 0:
                 best = min(best, a.elapsed_time(b))
             launches = prob.launch_count() - l0
-        row = dict(mode=mode, G=int(G), B=B, ms=best, solves_per_s=B / best * 1e3, launches=launches,
+        row = dict(mode=mode, G=int(G), B=B, W=int(W), ms=best, solves_per_s=B / best * 1e3, launches=launches,
                    converged=float((st.status == 1).double().mean().item()),
                    inner_mean=float(st.inner_iterations.double().mean().item()),
                    inner_max=int(st.inner_iterations.max().item()),
