@@ -45,6 +45,7 @@ struct MpcHandle {
   int32_t* rs_i = nullptr; size_t rs_i_cap = 0;
   void* rs_req = nullptr; size_t rs_req_cap = 0;
   double* rs_escr = nullptr; size_t rs_escr_cap = 0;
+  int32_t* rs_keys = nullptr; size_t rs_keys_cap = 0;  // transition buckets: counts [2][NKEY] + lists [2][NKEY][nt]
   unsigned* rs_counters = nullptr;                     // [8] device
   unsigned* rs_counters_host = nullptr;                // [64][4] pinned: every round's request counters of one chunk
   const char* round_log = nullptr;                     // MPCB_ROUND_LOG=path: per-round [grad requests, psi requests, T ms, E ms]
@@ -250,7 +251,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
   cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->dev);
-  cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_counters);
+  cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_keys); cudaFree(h->rs_counters);
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
   if (h->pin) cudaFreeHost(h->pin);
@@ -403,7 +404,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   //    lane's evaluation request and an evaluation launch over the compacted request lists.  The host
   //    enqueues rounds ahead of the GPU and reads the request counters every few dozen rounds to stop.
   // Tile width: spare lanes are spent on speculative line-search candidates (mpcb_solve.cuh).
-  const int block = 64;
+  int block = 64;
   // small batches: one asynchronous persistent launch; from a few thousand instances on the rounds win
   // (profiles/r01_round_mode.md: 218 vs 244 ms at B = 1024, 289 vs 413 ms at B = 4096, 2.6 vs 6.9 s at B = 65536)
   const int mode = h->mode_override >= 0 ? h->mode_override : (B >= 1024 ? 1 : 0);
@@ -422,8 +423,9 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     if (B * 8 <= (int64_t)h->num_sms * 8 * 32) G = 8;
   }
   if (h->tile_override > 0) G = h->tile_override;
-  // + box [2n] + the two-loop recursion scalars of the CTA's tiles [64 / G][2 mem]
-  const size_t box_smem = ((size_t)2 * k.n + (size_t)(64 / G) * 2 * sp->lbfgs_mem) * sizeof(double);
+  if (mode == 1) block = MPCB_ROUND_BLOCK;
+  // + box [2n] + the two-loop recursion scalars of the CTA's tiles [block / G][2 mem]
+  const size_t box_smem = ((size_t)2 * k.n + (size_t)(block / G) * 2 * sp->lbfgs_mem) * sizeof(double);
   smem += box_smem;
   if (smem > 200 * 1024) return fail(h, MPCB_E_UNSUPPORTED, "mpcb_solve: road table + L-BFGS scalars exceed shared memory");
   int64_t tiles_wanted = B;
@@ -431,6 +433,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   const int64_t max_blocks = lane_cap / block;
   if (mode == 0 && blocks > max_blocks) blocks = max_blocks;
   const int64_t ns = blocks * block, nt = ns / G;
+  // round mode: the transition grid covers every tile plus the padding of the buckets to whole warps
+  if (mode == 1) blocks = ((nt + (int64_t)MPCB_NKEY * (32 / G)) * G + block - 1) / block;
   const bool bounded = k.bounded != 0;
   const int stage_doubles = k.model_id == MPCB_MODEL_PACEJKA6 ? fm_stage_doubles<MPCB_MODEL_PACEJKA6>()
                                                               : fm_stage_doubles<MPCB_MODEL_KINEMATIC4>();
@@ -467,6 +471,10 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
       CK(cudaMallocHost((void**)&h->rs_counters_host, 64 * 4 * sizeof(unsigned)));
     }
     CK(cudaMemsetAsync(h->rs_counters, 0, 16 * sizeof(unsigned), st));
+    const size_t key_ints = (size_t)2 * MPCB_NKEY * (1 + (size_t)nt);
+    if ((rc = grow(h, &h->rs_keys, &h->rs_keys_cap, key_ints * sizeof(int32_t), st))) return rc;
+    CK(cudaMemsetAsync(h->rs_keys, 0, (size_t)2 * MPCB_NKEY * sizeof(int32_t), st));
+    a.key_cnt = h->rs_keys; a.key_list = h->rs_keys + 2 * MPCB_NKEY;
     char* rq = (char*)h->rs_req;
     a.req_b = (int64_t*)rq;
     a.req_p = (double**)(rq + ns8 * 8);
@@ -521,6 +529,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
       for (int i = 0; i < chunk; ++i, ++round) {
         a.round = (int)round;
         e.counters = h->rs_counters + 4 * (round & 1);
+        e.key_cnt_zero = a.key_cnt + MPCB_NKEY * (round & 1);
         e.trace = (trace_round >= 0 && round == trace_round) ? (long long*)h->dbg : nullptr;
         CK(cudaEventRecord(h->rs_ev[3 * i], st));
         if (k.model_id == MPCB_MODEL_PACEJKA6) {

@@ -64,11 +64,18 @@ struct SolveArgs {
   unsigned* counters;        // [2][4] by round parity: gradient requests, value requests, evaluation work counter, live tiles
   // Speculation window (tau candidates evaluated per round, 1 .. G-1): spec_w > 0 fixes it (MPCB_SPECW); 0 = picked on
   // the device from the number of tiles still solving (ctl[0], written by the previous round's evaluation launch).
+  // Tile order of the transition launches: tiles are bucketed by what they will do next (state + line-search phase)
+  // so that the tiles of a warp, and the warps that follow each other on an SM, run the same code.  key_cnt[parity]
+  // [MPCB_NKEY] and key_list[parity][MPCB_NKEY][nt] (tile indices): launch r reads parity r & 1 and fills the other.
+  int32_t* key_cnt;
+  int32_t* key_list;
   int spec_w;
   int spec_live_wide, spec_live_mid;  // live tiles up to which the window is G-1 wide / 3 wide (1 beyond)
   const unsigned* ctl;       // [4] device control words: [0] live tiles of the previous round
 };
 constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 26;
+constexpr int MPCB_NKEY = 16;       // transition buckets: one per SolveState, ST_LS_STEP split by phase
+constexpr int MPCB_ROUND_BLOCK = 128;  // lanes per CTA of a transition launch
 
 enum SolveState {
   ST_IDLE = 0, ST_START_PANOC, ST_INIT_G1, ST_LIP_DONE, ST_XHAT_REQ, ST_XHAT_DONE, ST_ITER_TOP, ST_FD_DONE,
@@ -99,7 +106,7 @@ struct TileMap {
 };
 
 template <int MODEL, int G, bool ROUND>
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(ROUND ? MPCB_ROUND_BLOCK : 64)
 k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   constexpr int NX = Fm<MODEL>::NX;
   constexpr int K = ROUND ? 0 : fm_stage_doubles<MODEL>();  // round mode: the stage Jacobians live in the evaluation kernel's scratch
@@ -107,20 +114,42 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   const int n = d.n, m = d.m, mem = sp.lbfgs_mem;
   double* sroad = smem;
   double* sbox = smem + (!ROUND && a.ra.in_smem ? a.ra.R * road_smem_doubles(d.S) : 0);  // lb[n], ub[n]
+  // ---- which tile does this group of G lanes run? ----
+  // persistent kernel: tile = position in the grid.  Round mode: launch r takes the tiles in the order launch r-1
+  // bucketed them (key_list), every bucket padded to whole warps; groups beyond the last live tile have none.
+  int64_t tile_sel = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+  bool notile = false;
   if constexpr (!ROUND) {
     fm_load_smem();
     if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
-  } else if (a.round > 0) {
-    // a CTA whose tiles have all finished leaves before any staging: late in a batch a handful of tiles is
-    // alive and the launch is thousands of such CTAs
-    const int64_t s0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (__syncthreads_and((a.si[s0] & 1024) != 0)) {
-      if (s0 == 0) {
-        unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
-        nx[0] = 0u; nx[1] = 0u; nx[2] = 0u; nx[3] = 0u;
+  } else {
+    constexpr int TPW = 32 / G;  // tiles per warp
+    if (a.round > 0) {
+      const int32_t* kc = a.key_cnt + MPCB_NKEY * (a.round & 1);
+      int64_t g = tile_sel, start = 0;
+      int key = -1;
+      int64_t off = 0;
+#pragma unroll 1
+      for (int kq = 0; kq < MPCB_NKEY; ++kq) {
+        const int64_t c = kc[kq];
+        const int64_t cp = (c + TPW - 1) / TPW * TPW;
+        if (key < 0 && g < start + cp) { key = kq; off = g - start; if (off >= c) key = MPCB_NKEY; }
+        start += cp;
       }
-      return;
+      // `start` = padded number of groups: a CTA past it has nothing to do (late in a batch: most of the grid)
+      if ((int64_t)blockIdx.x * (blockDim.x / G) >= start) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) {  // (no live tile at all: the batch is done)
+          unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
+          nx[0] = 0u; nx[1] = 0u; nx[2] = 0u; nx[3] = 0u;
+        }
+        return;
+      }
+      if (key < 0 || key >= MPCB_NKEY) notile = true;
+      else tile_sel = a.key_list[((int64_t)(a.round & 1) * MPCB_NKEY + key) * a.nt + off];
+    } else if (tile_sel >= a.nt) {
+      notile = true;
     }
+    if (notile) tile_sel = 0;
   }
   for (int i = threadIdx.x; i < n; i += blockDim.x) { sbox[i] = a.lb[i]; sbox[n + i] = a.ub[i]; }
   if constexpr (ROUND) __syncthreads();
@@ -131,12 +160,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   double* const s_ra = sbox + 2 * n + (threadIdx.x / G) * 2 * mem;
 
   const int64_t ns = a.ns, nt = a.nt;
-  const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
   const int l = lane % G;  // lane within the tile
   const int tbase = lane - l;
   const unsigned tmask = ((G >= 32) ? 0xffffffffu : ((1u << G) - 1u)) << tbase;
-  const int64_t tile = slot / G;
+  const int64_t tile = tile_sel;
+  const int64_t slot = tile * G + l;  // this lane's column in every lane-interleaved array
   const LaneMap M(n, d.N, NX, K, d.bounded != 0);
   const TileMap T(n, G, mem, m, d.bounded != 0);
   const int ne = T.np / G;  // tile-vector elements owned by each lane: e = l + G j
@@ -202,9 +231,9 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   X(ppsi) X(norm_e2) X(psi_n) X(psi_hat_n) X(gTp_n) X(pTp_n) X(L_n) X(gam_n) X(phi_n)
 #define MPCB_STATE_I(X) X(state) X(cl) X(cb) X(fd_lane) X(ge_row) X(ge_lane) X(k) X(no_prog) X(lb_idx) X(lb_full) X(hb) X(lsw) \
   X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for) X(lsW)
-  bool dead = false;  // round mode: this tile has no instance left
+  bool dead = notile;  // round mode: this group has no tile / its tile has no instance left
   if constexpr (ROUND) {
-    if (a.round > 0) {
+    if (a.round > 0 && !notile) {
       const int fl = a.si[slot];
       exhausted = fl & 1; fd_ready = fl & 2; c_valid = fl & 4; c_pend = fl & 8; c_rq = fl & 16; c_fb = fl & 32;
       c_acc = fl & 64; c_started = fl & 128; fd_done = fl & 256; c_needg = fl & 512;
@@ -964,7 +993,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       // ================= round mode: publish the request, save the registers, leave ===============
       // (the evaluation runs in k_eval_requests over the compacted request lists)
       unsigned* cnt = a.counters + 4 * (a.round & 1);
-      if (slot == 0) {  // the other parity's counters: last read by the previous evaluation launch
+      if (blockIdx.x == 0 && threadIdx.x == 0) {  // the other parity's counters: last read by the previous evaluation launch
         unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
         nx[0] = 0u; nx[1] = 0u; nx[2] = 0u; nx[3] = 0u;
       }
@@ -989,6 +1018,25 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         a.req_g[slot] = want == 3 ? WL(M.ST, l).p : evg.p;
         if (want == 2) { a.list_grad[bg + __popc(mg & below_me)] = (int32_t)slot; ++n_grad; }
         else { a.list_val[bv + __popc(mv & below_me)] = (int32_t)slot; if (want == 1) ++n_val; }
+      }
+      // ---- bucket the tile for the next transition launch: what it does there is decided by its state, and in
+      // ST_LS_STEP by whether it waits for psi(x̂+) (the round that usually ends the iteration: L-BFGS update, next
+      // direction, next candidates) or for the gradients of new candidates (prox steps only)
+      {
+        __shared__ int s_kcnt[MPCB_NKEY], s_kbase[MPCB_NKEY];
+        if (threadIdx.x < MPCB_NKEY) s_kcnt[threadIdx.x] = 0;
+        __syncthreads();
+        const bool rq_any = (__ballot_sync(tmask, c_rq) & tmask) != 0u;
+        const int key = state == ST_LS_STEP ? (rq_any ? (int)ST_LS_STEP : (int)ST_ALM_UPDATE + 1) : state;
+        int rank = -1;
+        if (l == 0 && !dead) rank = atomicAdd(&s_kcnt[key], 1);
+        __syncthreads();
+        int32_t* kc_out = a.key_cnt + MPCB_NKEY * ((a.round + 1) & 1);
+        if (threadIdx.x < MPCB_NKEY && s_kcnt[threadIdx.x] > 0)
+          s_kbase[threadIdx.x] = atomicAdd(&kc_out[threadIdx.x], s_kcnt[threadIdx.x]);
+        __syncthreads();
+        if (rank >= 0)
+          a.key_list[((int64_t)((a.round + 1) & 1) * MPCB_NKEY + key) * nt + s_kbase[key] + rank] = (int32_t)tile;
       }
       if (!was_dead) {  // tiles that were already dead keep their saved flags
         a.si[slot] = (int)exhausted | (int)fd_ready << 1 | (int)c_valid << 2 | (int)c_pend << 3 | (int)c_rq << 4 | (int)c_fb << 5 |
@@ -1062,6 +1110,7 @@ struct EvalArgs {
   const int32_t *list_grad, *list_val;
   unsigned* counters;       // this round's [4]
   unsigned* ctl;            // [4] control words read by the next transition launch: [0] live tiles
+  int32_t* key_cnt_zero;    // [MPCB_NKEY] bucket counts the next transition launch appends to (zeroed here)
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
   long long* trace;         // diagnostic (MPCB_EVAL_TRACE=round): per chunk [cycles, first slot] or null
   int split_ok;             // 0: never use the split evaluation (MPCB_SPLIT=0)
@@ -1087,6 +1136,7 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const Vec scr{e.escr + eslot, e.ens};
   const unsigned ng = e.counters[0], nv = e.counters[1];
   if (blockIdx.x == 0 && threadIdx.x == 0 && e.ctl) e.ctl[0] = e.counters[3];
+  if (blockIdx.x == 0 && threadIdx.x < MPCB_NKEY && e.key_cnt_zero) e.key_cnt_zero[threadIdx.x] = 0;
   const unsigned n_warps = gridDim.x * (blockDim.x >> 5);
   const unsigned cv = (nv + 31u) >> 5;
   // few gradient requests (every chunk still gets a warp slot of its own on half the sub-partitions): 8 lanes per
