@@ -205,6 +205,17 @@ int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const do
  * gamma_out is a DEVICE pointer [B]; B at most the last solve's batch. */
 int mpcb_last_final_gamma(MpcHandle* h, int64_t B, double* gamma_out, void* stream);
 
+/* Per-iteration trace in place of the reference's host progress callback (controller.py:23-24,38 prints info.ψ every
+ * PANOC iteration): mpcb_set_trace(h, cap) makes every later solve on the handle record psi at the top of each inner
+ * iteration (all PANOC runs of the ALM loop, in order) into a handle-owned buffer [B, cap]; cap = 0 turns it off.
+ * mpcb_last_trace copies it to a DEVICE buffer [B, cap]; iterations that were not reached hold NaN. */
+int mpcb_set_trace(MpcHandle* h, int32_t cap);
+int mpcb_last_trace(MpcHandle* h, int64_t B, double* trace_out, void* stream);
+
+/* alpaqa's stats['inner_convergence_failures'] (printed by controller.py:61) of the last solve on this handle: PANOC
+ * runs of the ALM loop that ended without Converged, per instance.  out is a DEVICE pointer [B] (int32). */
+int mpcb_last_inner_failures(MpcHandle* h, int64_t B, int32_t* out, void* stream);
+
 /* Bytes moved by the last mpcb_solve_host call (bench.py's e2e.h2d/d2h_bytes_per_step). */
 void mpcb_last_transfer_bytes(MpcHandle* h, int64_t* h2d, int64_t* d2h);
 

@@ -70,6 +70,9 @@ SIGNATURES = {
     "mpcb_value_grad_static": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "mpcb_solve": (C.c_int, [C.c_void_p, C.POINTER(MpcSolverParams), _I64] + [_P] * 15),
     "mpcb_solve_host": (C.c_int, [C.c_void_p, C.POINTER(MpcSolverParams), _I64] + [_P] * 14),
+    "mpcb_set_trace": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mpcb_last_trace": (C.c_int, [C.c_void_p, _I64, _P, _P]),
+    "mpcb_last_inner_failures": (C.c_int, [C.c_void_p, _I64, _P, _P]),
     "mpcb_last_final_gamma": (C.c_int, [C.c_void_p, _I64, _P, _P]),
     "mpcb_last_transfer_bytes": (None, [C.c_void_p, C.POINTER(_I64), C.POINTER(_I64)]),
     "mpcb_plant_step": (C.c_int, [C.c_void_p, _I64, _P, _P, _P, _P, _P]),

@@ -7,12 +7,14 @@ in the reference:
     x, y, stats = solver(problem, x, y)          # controller.py:57
 
 Differences, all deliberate: wall-clock caps ('max_time', controller.py:30,44) are accepted and ignored
-(they make results time-dependent); the per-iteration Python progress callback (controller.py:23-24,38)
-is accepted and never called (no host round trip inside the fused kernel); x / y / problem.param may
-carry a leading batch dimension.
+(they make results time-dependent); 'hessian_step_size_heuristic' (controller.py:32) is accepted, ignored and warned
+about once (alpaqa 0.0.1's rule is not recoverable here: SURVEY Appendix A 3c); the per-iteration Python progress
+callback (controller.py:23-24,38) is fed AFTER the solve from a per-iteration trace the kernel records (no host round
+trip inside the solver), for instance 0 of a batch; x / y / problem.param may carry a leading batch dimension.
 """
 import enum
 import time
+import warnings
 from datetime import timedelta
 
 import numpy as np
@@ -41,8 +43,12 @@ class PANOCStopCrit(enum.Enum):
 ProjGradNorm2 = PANOCStopCrit.ProjGradNorm2
 
 
-class StructuredPANOCLBFGSProgressInfo:  # type named by controller.py:23,49; never instantiated here
-    pass
+class StructuredPANOCLBFGSProgressInfo:
+    """What the reference's callback receives (controller.py:23-24 reads `.ψ`): one per inner iteration, built from
+    the kernel's trace buffer after the solve."""
+
+    def __init__(self, k=0, ψ=float("nan"), instance=0):
+        self.k, self.ψ, self.instance = k, ψ, instance
 
 
 class Box:
@@ -66,20 +72,48 @@ class Problem:
         self._mpc = None
         self._mpc_key = None
 
-    def mpc(self):
-        """The device-side problem (created on first use; rebuilt if D's finiteness pattern changes)."""
+    def mpc(self, road_mode=_ffi.ROAD_SHARED, n_roads=1):
+        """The device-side problem for one road layout (created on first use; rebuilt if D's finiteness pattern
+        changes).  The reference's only case — ONE centerline in `param` — is MPCB_ROAD_SHARED: the road is staged in
+        shared memory and the nearest-vertex scan is pruned.  A batch over a few distinct centerlines becomes a road
+        table; only a batch of many distinct centerlines pays for the per-instance layout."""
         from .solver import BatchedMpc
         Dl = np.asarray(self.D.lowerbound).reshape(self.N_horiz, self.nx)[0]
         Du = np.asarray(self.D.upperbound).reshape(self.N_horiz, self.nx)[0]
         bounded = bool(np.isfinite(Dl).any() or np.isfinite(Du).any())
-        key = (bounded, tuple(Dl), tuple(Du))
-        if self._mpc is None or key != self._mpc_key:
-            self._mpc = BatchedMpc(N=self.N_horiz, S=self.centerline_size, model_id=self.model_id,
-                                   road_mode=_ffi.ROAD_PER_INSTANCE, v_ref=self.v_ref, c=self.c, Ts=self.Ts,
-                                   flags=self.flags | (_ffi.FLAG_BOUNDED_D if bounded else 0), n_obs=self.n_obs,
-                                   D_lower=Dl, D_upper=Du)
-            self._mpc_key = key
-        return self._mpc
+        key = (bounded, tuple(Dl), tuple(Du), road_mode, n_roads)
+        if self._mpc is None:
+            self._mpc = {}
+        if key not in self._mpc:
+            self._mpc[key] = BatchedMpc(N=self.N_horiz, S=self.centerline_size, model_id=self.model_id,
+                                        road_mode=road_mode, n_roads=n_roads, v_ref=self.v_ref, c=self.c, Ts=self.Ts,
+                                        flags=self.flags | (_ffi.FLAG_BOUNDED_D if bounded else 0), n_obs=self.n_obs,
+                                        D_lower=Dl, D_upper=Du)
+        return self._mpc[key]
+
+
+MAX_TABLE_ROADS = 32
+
+
+def dedupe_roads(road, max_roads=MAX_TABLE_ROADS):
+    """(table [R, 2S], idx [B] int32) if the rows of `road` [B, 2S] take at most `max_roads` distinct values, else
+    None.  One vectorised pass per distinct road (the reference's callers pass one road, or a handful)."""
+    B = road.shape[0]
+    idx = np.full(B, -1, np.int32)
+    table = []
+    left = np.arange(B)
+    while left.size:
+        if len(table) == max_roads:
+            return None
+        r = road[left[0]]
+        same = (road[left] == r).all(axis=1)
+        idx[left[same]] = len(table)
+        table.append(r)
+        left = left[~same]
+    return np.ascontiguousarray(np.stack(table)), idx
+
+
+_warned_heuristic = False
 
 
 class StructuredPANOCLBFGSSolver:
@@ -103,8 +137,13 @@ class StructuredPANOCLBFGSSolver:
                           ("max_no_progress", "max_no_progress")):
             if k_py in pp:
                 setattr(sp, k_c, type(getattr(sp, k_c))(pp[k_py]))
-        # 'max_time' (controller.py:30), 'hessian_step_size_heuristic' (controller.py:32; rule not recoverable,
-        # SURVEY Appendix A) and 'print_interval' are accepted and ignored.
+        # 'max_time' (controller.py:30) and 'print_interval' are accepted and ignored.
+        global _warned_heuristic
+        if pp.get("hessian_step_size_heuristic", 0) and not _warned_heuristic:
+            _warned_heuristic = True
+            warnings.warn("mpcb200: panoc_params['hessian_step_size_heuristic'] is ignored (alpaqa 0.0.1's step-size rule is "
+                          "not recoverable; the canonical solver of SURVEY Appendix A runs without it): iteration counts "
+                          "can differ from alpaqa's", stacklevel=3)
         return sp
 
 
@@ -133,26 +172,50 @@ class ALMSolver:
         X = np.ascontiguousarray(np.atleast_2d(x)).copy()
         B, nx, S = X.shape[0], problem.nx, problem.centerline_size
         par = np.atleast_2d(np.asarray(problem.param, dtype=np.float64))
-        if par.shape[0] == 1 and B > 1:
-            par = np.broadcast_to(par, (B, par.shape[1]))
-        y0 = np.ascontiguousarray(par[:, :nx])
-        road = np.ascontiguousarray(par[:, nx:nx + 2 * S])
+        y0 = par[:, :nx]
+        if y0.shape[0] == 1 and B > 1:
+            y0 = np.broadcast_to(y0, (B, nx))
+        y0 = np.ascontiguousarray(y0)
         p = np.ascontiguousarray(par[0, nx + 2 * S:nx + 2 * S + _ffi.NP])
+        # road layout: one centerline for everybody (the reference's case) / a few / one per instance
+        roads = par[:, nx:nx + 2 * S]
+        road_idx = None
+        if roads.shape[0] == 1:
+            mpc, road = problem.mpc(_ffi.ROAD_SHARED), np.ascontiguousarray(roads[0])
+        else:
+            dd = dedupe_roads(roads)
+            if dd is None:
+                mpc, road = problem.mpc(_ffi.ROAD_PER_INSTANCE), np.ascontiguousarray(roads)
+            elif dd[0].shape[0] == 1:
+                mpc, road = problem.mpc(_ffi.ROAD_SHARED), dd[0][0]
+            else:
+                mpc, road, road_idx = problem.mpc(_ffi.ROAD_TABLE, dd[0].shape[0]), dd[0], dd[1]
         lam = None
         if y is not None:
             lam = np.ascontiguousarray(np.atleast_2d(np.asarray(y, dtype=np.float64))).copy()
-        mpc = problem.mpc()
         sp = self._params(problem.N_horiz)
-        X, lam, st = mpc.solve_host(y0, road, X, lam=lam, lb=np.asarray(problem.C.lowerbound, float),
+        cb = self.inner_solver._callback
+        cap = 0
+        if cb is not None:  # per-iteration psi of instance 0, replayed to the callback after the solve
+            cap = int(min(max(sp.max_iter, 1) * 8, 1 << 14))
+        mpc.set_trace(cap)
+        X, lam, st = mpc.solve_host(y0, road, X, lam=lam, road_idx=road_idx, lb=np.asarray(problem.C.lowerbound, float),
                                     ub=np.asarray(problem.C.upperbound, float), sp=sp, p=p)
+        ifail = mpc.last_inner_failures(B).cpu().numpy()
+        if cb is not None:
+            tr = mpc.last_trace(1)[0].cpu().numpy()
+            for k, v in enumerate(tr[:int(st.inner_iterations[0]) + int(st.outer_iterations[0])]):
+                if v == v:
+                    cb(StructuredPANOCLBFGSProgressInfo(k=k, ψ=float(v), instance=0))
         elapsed = timedelta(seconds=time.perf_counter() - t0)
         status = [SolverStatus(int(s)) for s in st.status]
+        extra = {"hessian_step_size_heuristic": "off (ignored)", "road_layout": {0: "shared", 1: "table", 2: "per_instance"}[mpc.desc.road_mode]}
         if batched:
             stats = {"status": status, "outer_iterations": st.outer_iterations.copy(),
                      "inner": {"iterations": st.inner_iterations.copy()}, "elapsed_time": elapsed,
-                     "inner_convergence_failures": np.zeros(B, int), "ε": st.residual.copy(), "ψ": st.psi.copy()}
+                     "inner_convergence_failures": ifail.astype(int), "ε": st.residual.copy(), "ψ": st.psi.copy(), **extra}
             return X, lam, stats
         stats = {"status": status[0], "outer_iterations": int(st.outer_iterations[0]),
                  "inner": {"iterations": int(st.inner_iterations[0])}, "elapsed_time": elapsed,
-                 "inner_convergence_failures": 0, "ε": float(st.residual[0]), "ψ": float(st.psi[0])}
+                 "inner_convergence_failures": int(ifail[0]), "ε": float(st.residual[0]), "ψ": float(st.psi[0]), **extra}
         return X[0], (None if lam is None else lam[0]), stats

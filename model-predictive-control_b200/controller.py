@@ -88,6 +88,61 @@ class MPCController:
         return self.U
 
 
+def mpc_controller(model, current_state, road, target_velocity, N=2, dt=0.1):
+    """reference controller.py:72-108 (legacy): explicit-Euler rollout of `model(x, u, t)` over N stages and
+    `scipy.optimize.minimize` (BFGS, finite-difference gradient) on cte / heading / speed penalties; returns the first
+    input.  Kept importable with the reference's semantics; NOT on the accelerated path (superseded by the
+    alpaqa controller).  `model` and `road` are the reference-named objects of mpcb200.dynamics / mpcb200.road, whose
+    evaluations run on the GPU.  One deliberate difference: the reference passes `np.array(x[0], x[1])` as the
+    position (controller.py:89), which raises a TypeError in NumPy; the position is built as `np.array([x[0], x[1]])`."""
+    from scipy.optimize import minimize
+
+    def cost_fn(u_flat, *args):
+        states, N, dt, current_state, road, target_velocity = args
+        cost = 0
+        u = u_flat.reshape(2, N)
+        cte_weight, heading_weight, velocity_weight = 100, 10, 10
+        for i in range(N):
+            if i == 0:
+                x = np.copy(current_state)
+            else:
+                x = x + model(states[i - 1], u[:, i - 1], dt * (i - 1)) * dt
+            states[i] = x
+            _, heading_error, cte = road.compute_errors(np.array([x[0], x[1]]), x[2])
+            velocity = np.sqrt(x[3] ** 2 + x[4] ** 2)
+            cost += cte_weight * cte ** 2 + heading_weight * heading_error ** 2 + velocity_weight * velocity
+        return cost
+
+    states = [None] * N
+    u_flat = np.zeros((N * 2,))
+    result = minimize(cost_fn, u_flat, args=(states, N, dt, np.asarray(current_state, dtype=np.float64), road, target_velocity))
+    return result.x.reshape(2, N)[:, 0]
+
+
+def mpc_controller_initial(model, current_state, target_state, N=2, dt=0.1):
+    """reference controller.py:111-135 (legacy): same rollout, cost = sum of squared distances to `target_state`."""
+    from scipy.optimize import minimize
+    target_state = np.asarray(target_state, dtype=np.float64)
+
+    def cost_fn(u_flat, *args):
+        states, target_state, N, dt = args
+        cost = 0
+        u = u_flat.reshape(2, N)
+        for i in range(N):
+            if i == 0:
+                x = np.copy(current_state)
+            else:
+                x = x + model(states[i - 1], u[:, i - 1], dt * (i - 1)) * dt
+            states[i] = x
+            cost += np.sum((x - target_state) ** 2)
+        return cost
+
+    states = [None] * N
+    u_flat = np.zeros((N * 2,))
+    result = minimize(cost_fn, u_flat, args=(states, target_state, N, dt))
+    return result.x.reshape(2, N)[:, 0]
+
+
 def straight_line_controller(current_state, road):
     """reference controller.py:138-156 (debug stub): constant full drive, no steering."""
     return np.array([1, 0])

@@ -52,6 +52,8 @@ struct MpcHandle {
   unsigned long long* queue = nullptr;
   double* zero_lam = nullptr; size_t zero_lam_cap = 0;
   double* gam = nullptr; size_t gam_cap = 0; int64_t gam_B = 0;  // final step sizes of the last solve
+  int32_t* ifail = nullptr; size_t ifail_cap = 0;                // inner convergence failures of the last solve
+  double* trace = nullptr; size_t trace_buf_cap = 0; int trace_cap = 0; int64_t trace_B = 0;  // mpcb_set_trace
   // staging for *_host entry points
   void* pin = nullptr; size_t pin_cap = 0;
   void* dev = nullptr; size_t dev_cap = 0;
@@ -250,7 +252,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
 
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
-  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->dev);
+  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->ifail); cudaFree(h->trace); cudaFree(h->dev);
   cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_keys); cudaFree(h->rs_counters);
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
@@ -445,10 +447,19 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   CK(cudaMemsetAsync(h->queue, 0, sizeof(unsigned long long), st));
   if ((rc = grow(h, &h->gam, &h->gam_cap, (size_t)B * sizeof(double), st))) return rc;
   h->gam_B = B;
+  if ((rc = grow(h, &h->ifail, &h->ifail_cap, (size_t)B * sizeof(int32_t), st))) return rc;
+  h->trace_B = 0;
+  if (h->trace_cap > 0) {
+    const size_t tb = (size_t)B * h->trace_cap * sizeof(double);
+    if ((rc = grow(h, &h->trace, &h->trace_buf_cap, tb, st))) return rc;
+    CK(cudaMemsetAsync(h->trace, 0xFF, tb, st));  // NaN = iteration not reached
+    h->trace_B = B;
+  }
   SolveArgs a;
   std::memset(&a, 0, sizeof(a));
   a.B = B; a.x0 = x0; a.p = p; a.obs = obs; a.lb = lb; a.ub = ub; a.ra = ra; a.U = U; a.lam = lambda;
-  a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res; a.gam_out = h->gam;
+  a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res; a.gam_out = h->gam; a.ifail_out = h->ifail;
+  a.trace = h->trace_cap > 0 ? h->trace : nullptr; a.trace_cap = h->trace_cap;
   a.ws = h->ws; a.wst = h->wst; a.ns = ns; a.nt = nt; a.queue = h->queue;
   a.dbg = nullptr;
   a.spec_w = h->spec_w; a.spec_live_wide = h->spec_live_wide; a.spec_live_mid = h->spec_live_mid; a.ctl = nullptr;
@@ -715,6 +726,34 @@ int64_t mpcb_debug_timers(MpcHandle* h, long long* out, int64_t max_warps) {
     std::fprintf(stderr, "[mpcb debug] model calls: fast path %llu, general path %llu (%.2f%%)\n", c[0], c[1],
                  100.0 * (double)c[1] / (double)(c[0] + c[1] + 1));
   return nw;
+}
+
+int mpcb_set_trace(MpcHandle* h, int32_t cap) {
+  if (!h || cap < 0 || cap > (1 << 20)) return fail(h, MPCB_E_ARG, "mpcb_set_trace: bad argument");
+  h->trace_cap = cap;
+  return MPCB_OK;
+}
+
+int mpcb_last_trace(MpcHandle* h, int64_t B, double* trace_out, void* stream) {
+  if (!h || !trace_out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_last_trace: bad argument");
+  if (B > h->trace_B || !h->trace || h->trace_cap <= 0) return fail(h, MPCB_E_ARG, "mpcb_last_trace: the last solve on this handle recorded no trace for that many instances (mpcb_set_trace)");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  if ((rc = enter(h, st))) return rc;
+  CK(cudaMemcpyAsync(trace_out, h->trace, (size_t)B * h->trace_cap * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  return leave(h, st);
+}
+
+int mpcb_last_inner_failures(MpcHandle* h, int64_t B, int32_t* out, void* stream) {
+  if (!h || !out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_last_inner_failures: bad argument");
+  if (B > h->gam_B || !h->ifail) return fail(h, MPCB_E_ARG, "mpcb_last_inner_failures: the last solve on this handle had fewer instances");
+  if (B == 0) return MPCB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  if ((rc = enter(h, st))) return rc;
+  CK(cudaMemcpyAsync(out, h->ifail, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  return leave(h, st);
 }
 
 int mpcb_last_final_gamma(MpcHandle* h, int64_t B, double* gamma_out, void* stream) {

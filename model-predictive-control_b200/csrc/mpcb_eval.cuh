@@ -67,6 +67,7 @@ MPCB_DEV RoadView road_view(const RoadArg& ra, const double* sroad, int S, int64
   RoadView r;
   if (ra.in_smem) {
     int ridx = ra.road_idx ? ra.road_idx[b] : 0;
+    ridx = ridx < 0 ? 0 : (ridx >= ra.R ? ra.R - 1 : ridx);  // an out-of-range index must not read past the staged table
     r.rx = nullptr; r.ry = nullptr; r.stride = 0;
     r.sbase = (unsigned)__cvta_generic_to_shared(sroad + (int64_t)ridx * road_smem_doubles(S));
     r.hbase = r.sbase + 16u * (unsigned)S;

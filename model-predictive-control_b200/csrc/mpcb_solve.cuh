@@ -44,6 +44,9 @@ struct SolveArgs {
   double *U, *lam;
   int32_t *status, *iters, *evals;
   double *psi, *res;
+  int32_t* ifail_out;  // [B] PANOC runs of the ALM loop that did not converge (alpaqa stats: inner_convergence_failures)
+  double* trace;       // optional [B, trace_cap]: psi at the top of every inner iteration (the progress callback's info.ψ)
+  int trace_cap;
   double* gam_out;  // [B] final step size gamma of every instance's last PANOC run (alpaqa's inner stats: final γ)
   double* ws;    // per-lane rows   [LaneMap.total, ns]
   double* wst;   // per-tile data   [TileMap.total, nt] (tile-vector region first, plain rows after)
@@ -73,7 +76,7 @@ struct SolveArgs {
   int spec_live_wide, spec_live_mid;  // live tiles up to which the window is G-1 wide / 3 wide (1 beyond)
   const unsigned* ctl;       // [4] device control words: [0] live tiles of the previous round
 };
-constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 26;
+constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 27;
 constexpr int MPCB_NKEY = 16;       // transition buckets: one per SolveState, ST_LS_STEP split by phase
 constexpr int MPCB_ROUND_BLOCK = 128;  // lanes per CTA of a transition launch
 
@@ -214,7 +217,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   unsigned specmask = 0;                 // candidates (by lane) whose FD speculation has been handed out
   double psi = 0, psi_hat = 0, gTp = 0, pTp = 0, L = 0, gam = 0, phi = 0, tau0 = 0, sigma = 0, hfd = 0, hh = 0;
   double eps_tol = 0, peps = 0, ppsi = 0, norm_e2 = 0;
-  int alm_i = 0, inner_total = 0, pstatus = 0;
+  int alm_i = 0, inner_total = 0, pstatus = 0, n_ifail = 0;
   unsigned long long mask0 = 0, mask1 = 0;  // inactive-set bitmask (n <= 128)
   auto mbit = [&](int j) { return j < 64 ? (mask0 >> j) & 1ull : (mask1 >> (j - 64)) & 1ull; };
   // ---- per-lane registers (this lane's candidate / evaluation request) ----
@@ -230,7 +233,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
 #define MPCB_STATE_D(X) X(psi) X(psi_hat) X(gTp) X(pTp) X(L) X(gam) X(phi) X(tau0) X(sigma) X(hfd) X(hh) X(eps_tol) X(peps) \
   X(ppsi) X(norm_e2) X(psi_n) X(psi_hat_n) X(gTp_n) X(pTp_n) X(L_n) X(gam_n) X(phi_n)
 #define MPCB_STATE_I(X) X(state) X(cl) X(cb) X(fd_lane) X(ge_row) X(ge_lane) X(k) X(no_prog) X(lb_idx) X(lb_full) X(hb) X(lsw) \
-  X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for) X(lsW)
+  X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for) X(lsW) X(n_ifail)
   bool dead = notile;  // round mode: this group has no tile / its tile has no instance left
   if constexpr (ROUND) {
     if (a.round > 0 && !notile) {
@@ -508,6 +511,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       a.psi[b] = d.debug >= 3 ? (double)t_rounds + 1e4 * dbg_fd + 1e8 * dbg_lemma + 1e12 * dbg_slide : ppsi;
       a.res[b] = peps;
       if (a.gam_out) a.gam_out[b] = gam;
+      if (a.ifail_out) a.ifail_out[b] = n_ifail;
     }
     n_val = 0; n_grad = 0; t_rounds = 0; dbg_fd = 0; dbg_lemma = 0; dbg_slide = 0;
   };
@@ -532,7 +536,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         }
         tsync();
         eps_tol = sp.eps0;
-        alm_i = 0; inner_total = 0; n_val = 0; n_grad = 0;
+        alm_i = 0; inner_total = 0; n_val = 0; n_grad = 0; n_ifail = 0;
         if (d.bounded) {
           for (int r = 0; r < m; ++r) { TR(T.SIG, r) = sp.Sigma0; TR(T.E1, r) = 0.0; }
         }
@@ -620,6 +624,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         phi = psi + pTp / (2.0 * gam) + gTp;
         state = ST_ITER_TOP;
       } else if (state == ST_ITER_TOP) {
+        if (a.trace && l == 0 && inner_total + k < a.trace_cap) a.trace[b * a.trace_cap + inner_total + k] = psi;
         double eps_k = sqrt(pTp);
         int stop = 0;
         if (!isfinite(eps_k)) stop = MPCB_STATUS_NOT_FINITE;
@@ -963,6 +968,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         state = ST_ALM_UPDATE;
       } else /* ST_ALM_UPDATE */ {
         bool inner_conv = pstatus == MPCB_STATUS_CONVERGED;
+        if (!inner_conv) ++n_ifail;
         int fin = 0;
         if (inner_conv && peps <= sp.eps_target && norm_e2 <= sp.delta_target) fin = MPCB_STATUS_CONVERGED;
         else if (alm_i + 1 == sp.alm_max_iter) fin = MPCB_STATUS_MAX_ITER;

@@ -36,6 +36,18 @@ def _dev_ptr(t, dtype, what):
     return C.c_void_p(t.data_ptr())
 
 
+def _on_device(fn):
+    """Run a BatchedMpc method with the handle's device current (launches and allocations of the library land on the
+    current device; the caller's current device may be another GPU)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(self, *args, **kw):
+        with torch.cuda.device(self.device):
+            return fn(self, *args, **kw)
+    return wrapper
+
+
 class BatchedMpc:
     """One problem description (model, horizon, road layout, cost terms) bound to the current CUDA device."""
 
@@ -111,6 +123,7 @@ class BatchedMpc:
         return self._t(lb), self._t(-lb)
 
     # ---- hot-path operations --------------------------------------------------------------------
+    @_on_device
     def dynamics(self, x, u, clip=False, p=None):
         x, u = self._t(x).reshape(-1, self.nx), self._t(u).reshape(-1, 2)
         out = torch.empty_like(x)
@@ -121,6 +134,7 @@ class BatchedMpc:
                    self._h, "mpcb_dynamics")
         return out
 
+    @_on_device
     def plant_step(self, x, u, p=None):
         x, u = self._t(x).reshape(-1, self.nx), self._t(u).reshape(-1, 2)
         out = torch.empty_like(x)
@@ -131,6 +145,7 @@ class BatchedMpc:
                    self._h, "mpcb_plant_step")
         return out
 
+    @_on_device
     def road_errors(self, pos, heading, road, road_idx=None, normalised=False):
         pos, heading, road = self._t(pos).reshape(-1, 2), self._t(heading).reshape(-1), self._t(road)
         B = pos.shape[0]
@@ -145,6 +160,7 @@ class BatchedMpc:
                                               self._stream()), self._h, "mpcb_road_errors")
         return idx, err
 
+    @_on_device
     def bezier_sample(self, ctrl):
         ctrl = self._t(ctrl).reshape(-1, 12)
         out = torch.empty(ctrl.shape[0], 2 * self.S, dtype=torch.float64, device=self.device)
@@ -161,6 +177,7 @@ class BatchedMpc:
         p = self.p if p is None else self._t(p)
         return x0, road, road_idx, obs, p
 
+    @_on_device
     def rollout(self, x0, U, road, road_idx=None, obs=None, p=None):
         """model.simulate + cost sum: returns (states [B,N,nx], nearest idx [B,N], cost [B])."""
         x0, road, road_idx, obs, p = self._common(x0, road, road_idx, obs, p)
@@ -177,6 +194,7 @@ class BatchedMpc:
                                           _dev_ptr(cost, f64, "cost"), self._stream()), self._h, "mpcb_rollout")
         return states, idx, cost
 
+    @_on_device
     def value_grad(self, x0, U, road, road_idx=None, obs=None, lam=None, Sigma=None, p=None, out=None):
         """psi and grad_U psi (generated-C f + grad_f)."""
         x0, road, road_idx, obs, p = self._common(x0, road, road_idx, obs, p)
@@ -214,6 +232,7 @@ class BatchedMpc:
                 _dev_ptr(grad, f64, "grad"), self._stream()), self._h, "mpcb_value_grad_static")
         return cost, grad
 
+    @_on_device
     def solve(self, x0, road, U, lam=None, road_idx=None, obs=None, lb=None, ub=None, sp=None, p=None):
         """The MPC step's NLP solve (controller.py:57).  U (and lam) are updated IN PLACE (warm start
         in, solution out) and also returned together with per-instance statistics."""
@@ -272,6 +291,28 @@ class BatchedMpc:
                                                  hp(obs), hp(lb), hp(ub), hp(U), hp(lam), hp(status), hp(iters),
                                                  hp(evals), hp(psi), hp(res)), self._h, "mpcb_solve_host")
         return U, lam, SolveStats(status, iters[:, 0], iters[:, 1], evals[:, 0], evals[:, 1], psi, res)
+
+    def set_trace(self, cap):
+        """Record psi at the top of every inner iteration of later solves (0 = off): the reference's progress callback."""
+        _ffi.check(self._lib.mpcb_set_trace(self._h, int(cap)), self._h, "mpcb_set_trace")
+        self._trace_cap = int(cap)
+
+    def last_trace(self, B):
+        """[B, cap] psi per inner iteration of the last solve (NaN where an instance had already stopped)."""
+        cap = getattr(self, "_trace_cap", 0)
+        out = torch.empty(B, cap, dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _ffi.check(self._lib.mpcb_last_trace(self._h, B, _dev_ptr(out, torch.float64, "trace"), self._stream()),
+                       self._h, "mpcb_last_trace")
+        return out
+
+    def last_inner_failures(self, B):
+        """[B] int32: PANOC runs of the last solve's ALM loops that did not converge (alpaqa: inner_convergence_failures)."""
+        out = torch.empty(B, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _ffi.check(self._lib.mpcb_last_inner_failures(self._h, B, _dev_ptr(out, torch.int32, "out"), self._stream()),
+                       self._h, "mpcb_last_inner_failures")
+        return out
 
     def last_final_gamma(self, B):
         """[B] final PANOC step sizes of the last solve on this handle (alpaqa's inner stats `final γ`)."""
