@@ -205,6 +205,24 @@ int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const do
  * gamma_out is a DEVICE pointer [B]; B at most the last solve's batch. */
 int mpcb_last_final_gamma(MpcHandle* h, int64_t B, double* gamma_out, void* stream);
 
+/* Game-theoretic lane-change decision for a batch of scenarios: replaces Car.get_total_payoff for target lanes 1 and 2
+ * (game_theory.py:205-244, with get_safety_payoff :155-176, get_safety_distance :115-153, get_velocity_payoff :178-189
+ * and the car-behind term that reads the module-global ego, :222-233), the decision of the reference's sweep
+ * (:377-379: change when the lane-2 payoff is larger) and get_bezier_control_points towards the car in front in ego's
+ * lane (:92-113, i = 5).  ego [B,3] and cars [B,M,3] are DEVICE arrays of (x, v, lane) records; lane <= 0 marks an empty
+ * slot.  car_params: HOST pointer to the 11 Car constants L, W, l, theta_max, tlc, td, ti, tau, a_max, h, Lf
+ * (game_theory.py:23-56) or NULL for the defaults.  Outputs (device): payoff_out [B,2]; decision_out [B] (1 = change to
+ * lane 2; nullable); ctrl_out [B,12] = Px0..5, Py0..5 relative to ego (NaN when nobody is in front or the speeds are
+ * equal; nullable) — the layout MPCB_ROAD_BEZIER takes; tca_out [B] (nullable). */
+void mpcb_default_car_params(double* c11);
+int mpcb_game_payoff(MpcHandle* h, int64_t B, int32_t M, const double* ego, const double* cars, const double* car_params,
+                     double* payoff_out, int32_t* decision_out, double* ctrl_out, double* tca_out, void* stream);
+
+/* Per-solve latency of the last solve on this handle (the metric's "p50 solve latency"; alpaqa reports elapsed_time per
+ * solve, controller.py:60): out is a DEVICE buffer of B + 1 uint64 — the GPU's %globaltimer (ns) at which instance b
+ * returned its answer, and in out[B] the time the solve started on the GPU.  B must equal the last solve's batch. */
+int mpcb_last_finish_ns(MpcHandle* h, int64_t B, uint64_t* out, void* stream);
+
 /* Per-iteration trace in place of the reference's host progress callback (controller.py:23-24,38 prints info.ψ every
  * PANOC iteration): mpcb_set_trace(h, cap) makes every later solve on the handle record psi at the top of each inner
  * iteration (all PANOC runs of the ALM loop, in order) into a handle-owned buffer [B, cap]; cap = 0 turns it off.

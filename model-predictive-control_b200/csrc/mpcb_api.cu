@@ -12,6 +12,7 @@
 #include <vector>
 #include "mpcb_kernels.cuh"
 #include "mpcb_solve.cuh"
+#include "mpcb_game.cuh"
 
 using namespace mpcb;
 
@@ -52,6 +53,7 @@ struct MpcHandle {
   unsigned long long* queue = nullptr;
   double* zero_lam = nullptr; size_t zero_lam_cap = 0;
   double* gam = nullptr; size_t gam_cap = 0; int64_t gam_B = 0;  // final step sizes of the last solve
+  unsigned long long* fin = nullptr; size_t fin_cap = 0;          // finish stamps of the last solve [B + 1]
   int32_t* ifail = nullptr; size_t ifail_cap = 0;                // inner convergence failures of the last solve
   double* trace = nullptr; size_t trace_buf_cap = 0; int trace_cap = 0; int64_t trace_B = 0;  // mpcb_set_trace
   // staging for *_host entry points
@@ -252,7 +254,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
 
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
-  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->ifail); cudaFree(h->trace); cudaFree(h->dev);
+  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->fin); cudaFree(h->ifail); cudaFree(h->trace); cudaFree(h->dev);
   cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_keys); cudaFree(h->rs_counters);
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
@@ -448,6 +450,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   if ((rc = grow(h, &h->gam, &h->gam_cap, (size_t)B * sizeof(double), st))) return rc;
   h->gam_B = B;
   if ((rc = grow(h, &h->ifail, &h->ifail_cap, (size_t)B * sizeof(int32_t), st))) return rc;
+  if ((rc = grow(h, &h->fin, &h->fin_cap, (size_t)(B + 1) * sizeof(unsigned long long), st))) return rc;
+  CK(cudaMemsetAsync(h->fin, 0xFF, (size_t)(B + 1) * sizeof(unsigned long long), st));
   h->trace_B = 0;
   if (h->trace_cap > 0) {
     const size_t tb = (size_t)B * h->trace_cap * sizeof(double);
@@ -458,7 +462,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   SolveArgs a;
   std::memset(&a, 0, sizeof(a));
   a.B = B; a.x0 = x0; a.p = p; a.obs = obs; a.lb = lb; a.ub = ub; a.ra = ra; a.U = U; a.lam = lambda;
-  a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res; a.gam_out = h->gam; a.ifail_out = h->ifail;
+  a.status = status; a.iters = iters; a.evals = evals; a.psi = psi; a.res = res; a.gam_out = h->gam; a.ifail_out = h->ifail; a.fin_ns = h->fin;
   a.trace = h->trace_cap > 0 ? h->trace : nullptr; a.trace_cap = h->trace_cap;
   a.ws = h->ws; a.wst = h->wst; a.ns = ns; a.nt = nt; a.queue = h->queue;
   a.dbg = nullptr;
@@ -726,6 +730,37 @@ int64_t mpcb_debug_timers(MpcHandle* h, long long* out, int64_t max_warps) {
     std::fprintf(stderr, "[mpcb debug] model calls: fast path %llu, general path %llu (%.2f%%)\n", c[0], c[1],
                  100.0 * (double)c[1] / (double)(c[0] + c[1] + 1));
   return nw;
+}
+
+void mpcb_default_car_params(double* c11) {  // game_theory.py:23-56
+  const double v[11] = {4.2, 1.8, 3.0, 3.2 / 180.0 * 3.14159265358979323846, 5.17, 1.2, 0.15, 0.9, 7.0, 3.75, 1.0};
+  for (int i = 0; i < 11; ++i) c11[i] = v[i];
+}
+
+int mpcb_game_payoff(MpcHandle* h, int64_t B, int32_t M, const double* ego, const double* cars, const double* car_params,
+                     double* payoff_out, int32_t* decision_out, double* ctrl_out, double* tca_out, void* stream) {
+  if (!h || B < 0 || M < 0 || M > 64) return fail(h, MPCB_E_ARG, "mpcb_game_payoff: bad argument (0 <= M <= 64)");
+  if (B == 0) return MPCB_OK;
+  if (!ego || (!cars && M > 0) || !payoff_out) return fail(h, MPCB_E_ARG, "mpcb_game_payoff: null argument");
+  double v[11];
+  mpcb_default_car_params(v);
+  if (car_params) for (int i = 0; i < 11; ++i) v[i] = car_params[i];  // HOST pointer, like MpcSolverParams
+  GamePar c{v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10]};
+  cudaStream_t st = (cudaStream_t)stream;
+  k_game_payoff<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(B, M, c, ego, cars, payoff_out, decision_out, ctrl_out, tca_out);
+  h->launches++;
+  CK(cudaGetLastError());
+  return MPCB_OK;
+}
+
+int mpcb_last_finish_ns(MpcHandle* h, int64_t B, uint64_t* out, void* stream) {
+  if (!h || !out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_last_finish_ns: bad argument");
+  if (B != h->gam_B || !h->fin) return fail(h, MPCB_E_ARG, "mpcb_last_finish_ns: B must be the batch of the last solve on this handle");
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  if ((rc = enter(h, st))) return rc;
+  CK(cudaMemcpyAsync(out, h->fin, (size_t)(B + 1) * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
+  return leave(h, st);
 }
 
 int mpcb_set_trace(MpcHandle* h, int32_t cap) {

@@ -44,6 +44,7 @@ struct SolveArgs {
   double *U, *lam;
   int32_t *status, *iters, *evals;
   double *psi, *res;
+  unsigned long long* fin_ns;  // optional [B + 1]: %globaltimer (ns) when instance b finished; [B] = start of the solve
   int32_t* ifail_out;  // [B] PANOC runs of the ALM loop that did not converge (alpaqa stats: inner_convergence_failures)
   double* trace;       // optional [B, trace_cap]: psi at the top of every inner iteration (the progress callback's info.ψ)
   int trace_cap;
@@ -117,6 +118,11 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   const int n = d.n, m = d.m, mem = sp.lbfgs_mem;
   double* sroad = smem;
   double* sbox = smem + (!ROUND && a.ra.in_smem ? a.ra.R * road_smem_doubles(d.S) : 0);  // lb[n], ub[n]
+  if (a.fin_ns && threadIdx.x == 0 && (!ROUND || a.round == 0)) {  // start of the solve: earliest CTA of the first launch
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    atomicMin(&a.fin_ns[a.B], t);
+  }
   // ---- which tile does this group of G lanes run? ----
   // persistent kernel: tile = position in the grid.  Round mode: launch r takes the tiles in the order launch r-1
   // bucketed them (key_list), every bucket padded to whole warps; groups beyond the last live tile have none.
@@ -511,6 +517,11 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       a.psi[b] = d.debug >= 3 ? (double)t_rounds + 1e4 * dbg_fd + 1e8 * dbg_lemma + 1e12 * dbg_slide : ppsi;
       a.res[b] = peps;
       if (a.gam_out) a.gam_out[b] = gam;
+      if (a.fin_ns) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.fin_ns[b] = t;
+      }
       if (a.ifail_out) a.ifail_out[b] = n_ifail;
     }
     n_val = 0; n_grad = 0; t_rounds = 0; dbg_fd = 0; dbg_lemma = 0; dbg_slide = 0;

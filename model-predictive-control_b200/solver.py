@@ -292,6 +292,36 @@ class BatchedMpc:
                                                  hp(evals), hp(psi), hp(res)), self._h, "mpcb_solve_host")
         return U, lam, SolveStats(status, iters[:, 0], iters[:, 1], evals[:, 0], evals[:, 1], psi, res)
 
+    @_on_device
+    def game_payoff(self, ego, cars, car_params=None):
+        """game_theory.py:205-244 for a batch: ego [B,3], cars [B,M,3] of (x, v, lane) -> (payoff [B,2], decision [B] int32,
+        ctrl [B,12], tca [B]) on the device (mpcb_game_payoff)."""
+        ego = self._t(ego).reshape(-1, 3)
+        B = ego.shape[0]
+        cars = self._t(cars).reshape(B, -1, 3)
+        M = cars.shape[1]
+        f64 = torch.float64
+        payoff = torch.empty(B, 2, dtype=f64, device=self.device)
+        decision = torch.empty(B, dtype=torch.int32, device=self.device)
+        ctrl = torch.empty(B, 12, dtype=f64, device=self.device)
+        tca = torch.empty(B, dtype=f64, device=self.device)
+        cp = None if car_params is None else np.ascontiguousarray(car_params, np.float64)
+        _ffi.check(self._lib.mpcb_game_payoff(self._h, B, M, _dev_ptr(ego, f64, "ego"), _dev_ptr(cars, f64, "cars"),
+                                              None if cp is None else C.c_void_p(cp.ctypes.data),
+                                              _dev_ptr(payoff, f64, "payoff"), _dev_ptr(decision, torch.int32, "decision"),
+                                              _dev_ptr(ctrl, f64, "ctrl"), _dev_ptr(tca, f64, "tca"), self._stream()),
+                   self._h, "mpcb_game_payoff")
+        return payoff, decision, ctrl, tca
+
+    def last_solve_latency_ms(self, B):
+        """[B] milliseconds from the start of the last solve on the GPU to the moment each instance returned its answer
+        (GPU %globaltimer stamps written by the kernels)."""
+        out = torch.empty(B + 1, dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            _ffi.check(self._lib.mpcb_last_finish_ns(self._h, B, C.c_void_p(out.data_ptr()), self._stream()),
+                       self._h, "mpcb_last_finish_ns")
+        return (out[:B] - out[B]).double() * 1e-6
+
     def set_trace(self, cap):
         """Record psi at the top of every inner iteration of later solves (0 = off): the reference's progress callback."""
         _ffi.check(self._lib.mpcb_set_trace(self._h, int(cap)), self._h, "mpcb_set_trace")

@@ -95,3 +95,24 @@ def lane_change_batch(B, N=40, S=100, seed=3, n_obs=2):
         obs[:, o, 4] = rng.uniform(-0.5, 0.5, B)
     U0 = np.tile([0.0, 0.0], (B, N))
     return dict(x0=np.ascontiguousarray(x0), ctrl=ctrl, obs=obs, U0=np.ascontiguousarray(U0))
+
+
+def game_pairs(P, seed=4, h=3.75):
+    """Config 4: P two-vehicle lane-change scenarios around reference game_theory.py:247-349 (`get_cars_test_1..3`: ego in
+    lane 1 closing in on a slow car, faster traffic in lane 2), scaled to the Kinematic-4 lane-change setting.
+
+    Vehicles are stored [A_0..A_{P-1}, B_0..B_{P-1}] (opponent of v is (v + P) mod 2P):  A_i drives in lane 1 (y = 0) behind
+    a slow lead car; B_i drives in lane 2 (y = h) behind A_i and faster.  Returns dict(x0 [2P,4] = (x, y, phi, v),
+    lead [2P,3] = (x, v, lane) of each vehicle's scenario lead car, U0 [2P, 2N] is left to the caller)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    vA = rng.uniform(15, 25, P)
+    xA = rng.uniform(0, 2, P)
+    lead_x = xA + rng.uniform(35, 70, P)
+    lead_v = vA - rng.uniform(5, 12, P)
+    xB = xA - rng.uniform(8, 30, P)
+    vB = vA + rng.uniform(-2, 5, P)
+    x0 = np.zeros((2 * P, 4))
+    x0[:P] = np.stack([xA, rng.uniform(-0.2, 0.2, P), rng.uniform(-0.02, 0.02, P), vA], axis=1)
+    x0[P:] = np.stack([xB, h + rng.uniform(-0.2, 0.2, P), rng.uniform(-0.02, 0.02, P), vB], axis=1)
+    lead = np.stack([lead_x, lead_v, np.ones(P)], axis=1)
+    return dict(x0=np.ascontiguousarray(x0), lead=np.ascontiguousarray(np.concatenate([lead, lead])), h=h)

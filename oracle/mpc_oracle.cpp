@@ -4,6 +4,7 @@
 #include <omp.h>
 #include <cstdio>
 #include "orc_solver.hpp"
+#include "orc_game.hpp"
 
 using namespace orc;
 
@@ -199,6 +200,29 @@ void orc_fb_residual_batch(const MpcProblemDesc* d, int64_t B, const double* x0,
       }
       res_out[b] = std::sqrt(s);
       if (psi_out) psi_out[b] = psi;
+    }
+  }
+}
+
+// game_theory.py:205-244 for a batch: ego [B,3] and cars [B,M,3] as (x, v, lane); payoff [B,2] for target lanes 1, 2;
+// decision [B] = 1 when lane 2 pays more (game_theory.py:377-379); ctrl [B,12] / tca [B] = get_bezier_control_points
+// towards the car in front in ego's lane (NaN when there is none or the speeds are equal).
+void orc_game_payoff_batch(int64_t B, int M, const double* ego, const double* cars, const double* car_par11,
+                           double* payoff, int32_t* decision, double* ctrl, double* tca) {
+  CarPar c = car_defaults();
+  if (car_par11) c = CarPar{car_par11[0], car_par11[1], car_par11[2], car_par11[3], car_par11[4], car_par11[5],
+                            car_par11[6], car_par11[7], car_par11[8], car_par11[9], car_par11[10]};
+  for (int64_t b = 0; b < B; ++b) {
+    CarRec e{ego[3 * b], ego[3 * b + 1], (int)ego[3 * b + 2]};
+    std::vector<CarRec> cs(M);
+    for (int k = 0; k < M; ++k) cs[k] = CarRec{cars[(b * M + k) * 3], cars[(b * M + k) * 3 + 1], (int)cars[(b * M + k) * 3 + 2]};
+    payoff[2 * b] = total_payoff(c, e, cs.data(), M, 1);
+    payoff[2 * b + 1] = total_payoff(c, e, cs.data(), M, 2);
+    if (decision) decision[b] = payoff[2 * b + 1] > payoff[2 * b] ? 1 : 0;
+    if (ctrl) {
+      const int f = car_in_front(e, cs.data(), M, -1, nullptr, e.lane);
+      if (f >= 0 && e.v != cs[f].v) lane_change_points(c, e, cs[f], 5.0, ctrl + 12 * b, tca + b);
+      else { for (int i = 0; i < 12; ++i) ctrl[12 * b + i] = NAN; tca[b] = NAN; }
     }
   }
 }

@@ -238,6 +238,20 @@ def fb_residual(desc, x0, U, road, gamma, p=DEFAULT_P, road_idx=None, obs=None, 
     return res, psi
 
 
+def game_payoff(ego, cars, car_par=None):
+    """game_theory.py:205-244 batched: ego [B,3], cars [B,M,3] as (x, v, lane; lane 0 = no car in that slot) ->
+    dict(payoff [B,2], decision [B], ctrl [B,12], tca [B])."""
+    ego = f64(ego).reshape(-1, 3)
+    B = ego.shape[0]
+    cars = f64(cars).reshape(B, -1, 3)
+    M = cars.shape[1]
+    payoff, decision = np.zeros((B, 2)), np.zeros(B, np.int32)
+    ctrl, tca = np.zeros((B, 12)), np.zeros(B)
+    lib().orc_game_payoff_batch(C.c_int64(B), C.c_int(M), _p(ego), _p(cars), _p(None if car_par is None else f64(car_par)),
+                                _p(payoff), _p(decision), _p(ctrl), _p(tca))
+    return dict(payoff=payoff, decision=decision, ctrl=ctrl, tca=tca)
+
+
 def count_ops(desc, x0, U, road, p=DEFAULT_P, obs=None):
     counts = (C.c_longlong * 4)()
     lib().orc_count_ops(C.byref(desc), _p(f64(x0)), _p(f64(U)), _p(f64(p)), _p(f64(road)),

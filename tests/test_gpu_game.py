@@ -1,0 +1,83 @@
+"""GPU: the game-theory payoff layer (reference game_theory.py:115-244, :92-113) through the C ABI
+(mpcb_game_payoff) against the reference-generated golden vectors and the oracle, and config 4 with the decision layer."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def mp():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("these tests need a CUDA device (there is no CPU fallback to test instead)")
+    import mpcb200
+    return mpcb200
+
+
+def test_payoff_kernel_matches_reference_golden(mp):
+    g = json.load(open(os.path.join(HERE, "golden", "reference_game_theory.json")))
+    cases, M = g["cases"], 8
+    ego = np.array([c["ego"] for c in cases], dtype=float)
+    cars = np.zeros((len(cases), M, 3))
+    for i, c in enumerate(cases):
+        cars[i, :len(c["cars"])] = c["cars"]
+    prob = mp.BatchedMpc(N=12, S=100)
+    payoff, decision, ctrl, tca = (t.cpu().numpy() for t in prob.game_payoff(ego, cars))
+    ref = np.array([c["payoff"] for c in cases])
+    np.testing.assert_allclose(payoff, ref, rtol=1e-13, atol=1e-14)
+    assert payoff[0] == pytest.approx([0.7999999999999999, 1.0365591188311774], rel=1e-15)   # SURVEY Appendix B, test-1
+    assert (decision == (ref[:, 1] > ref[:, 0])).all()
+    has = np.array(["P" in c for c in cases])
+    P = np.array([np.array(c["P"]).ravel() for c in cases if "P" in c])
+    np.testing.assert_allclose(ctrl[has], P, rtol=1e-13, atol=1e-13)
+    np.testing.assert_allclose(tca[has], [c["tca"] for c in cases if "P" in c], rtol=1e-13)
+    assert np.isnan(ctrl[~has]).all() and np.isnan(tca[~has]).all()
+
+
+def test_payoff_kernel_matches_oracle_on_a_batch(mp, orc):
+    rng = np.random.default_rng(12)
+    B, M = 4099, 6   # ragged
+    ego = np.stack([rng.uniform(-5, 5, B), rng.uniform(3, 25, B), rng.integers(1, 3, B)], axis=1).astype(float)
+    cars = np.stack([rng.uniform(-80, 100, (B, M)), rng.uniform(0, 28, (B, M)) * (rng.random((B, M)) > 0.1),
+                     rng.integers(0, 3, (B, M))], axis=2).astype(float)   # lane 0 = empty slot
+    prob = mp.BatchedMpc(N=12, S=100)
+    payoff, decision, ctrl, tca = (t.cpu().numpy() for t in prob.game_payoff(ego, cars))
+    r = orc.game_payoff(ego, cars)
+    np.testing.assert_allclose(payoff, r["payoff"], rtol=1e-12, atol=1e-13)
+    # a decision can only differ where the two payoffs are equal to rounding
+    diff = decision != r["decision"]
+    assert (np.abs(r["payoff"][diff, 1] - r["payoff"][diff, 0]) < 1e-12).all()
+    fin = np.isfinite(r["ctrl"]).all(axis=1)
+    assert (np.isfinite(ctrl).all(axis=1) == fin).all()
+    np.testing.assert_allclose(ctrl[fin], r["ctrl"][fin], rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(tca[fin], r["tca"][fin], rtol=1e-12)
+
+
+def test_config4_with_the_decision_layer(mp):
+    """Config 4 as BASELINE.json states it: payoff -> lane choice -> Bezier path -> MPC against the other vehicle's
+    announced trajectory, iterated; one rank (the exchange is the identity).  Deterministic, converging solves, both lane
+    decisions occur, and the best-response iteration settles (the trajectories stop changing)."""
+    import torch
+    from mpcb200 import scenarios as sc, workloads as wl
+    P, N = 64, 20
+    nv = 2 * P
+    w4 = wl.game_pairs(P, seed=4)
+    prob = mp.BatchedMpc(N=N, S=100, model_id=1, road_mode=mp.ROAD_BEZIER, flags=mp.FLAG_LANE | mp.FLAG_OBST, n_obs=2,
+                         v_ref=20.0)
+    r1 = sc.best_response_rounds(prob, w4["x0"], None, nv, rounds=5, cars=w4)
+    r2 = sc.best_response_rounds(prob, w4["x0"], None, nv, rounds=5, cars=w4)
+    assert torch.equal(r1["U"], r2["U"]) and torch.equal(r1["traj"], r2["traj"]) and torch.equal(r1["target"], r2["target"])
+    conv = (r1["status"].cpu().numpy() == 1).mean()
+    tg = r1["target"].cpu().numpy()
+    print(f"config 4 (decision layer): converged {conv:.3f}; lane-2 targets per round {[float((t == 2).mean()) for t in tg]}; "
+          f"lane changes {r1['lane_change_frac']:.2f}; trajectory change per round {r1['delta']}")
+    assert conv > 0.9
+    assert 0.05 < (tg[-1][:P] == 2).mean() <= 1.0     # some A vehicles decide to overtake
+    assert np.isfinite(r1["payoff"].cpu().numpy()).all()
+    # the iteration settles: the change between the last two rounds is far below the first response
+    assert r1["delta"][-1] <= 0.5 * max(r1["delta"][1], 1e-9) + 1e-6

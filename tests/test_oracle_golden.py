@@ -94,3 +94,28 @@ def test_potentials(orc, golden):
         assert orc.u_rbd(c["y"], c["y_br"], c["y_bl"]) == pytest.approx(c["val"], rel=1e-15)
     for c in golden["event_state"]:
         assert orc.event_state(c["x"], c["u_x"], c["a"], c["t0"], c["t1"]) == c["val"]
+
+
+def test_game_theory_payoffs_match_reference(orc):
+    """game_theory.py:115-244 (`get_total_payoff` for lanes 1 and 2 incl. the car-behind term and the module-global ego,
+    the lane decision, `get_bezier_control_points`) against vectors produced by the reference's own code
+    (tests/golden/gen_golden_game.py): 330 cases incl. SURVEY Appendix B's test-1 payoffs."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_game_theory.json")))
+    assert g["cases"][0]["payoff"] == [0.7999999999999999, 1.0365591188311774]   # SURVEY Appendix B
+    M = 8
+    n_ctrl = 0
+    for c in g["cases"]:
+        cars = np.zeros((M, 3))
+        cars[:len(c["cars"])] = c["cars"]
+        r = orc.game_payoff(np.array([c["ego"]]), cars[None])
+        np.testing.assert_allclose(r["payoff"][0], c["payoff"], rtol=1e-14, atol=1e-15)
+        assert r["decision"][0] == int(c["payoff"][1] > c["payoff"][0])
+        if "P" in c:
+            np.testing.assert_allclose(r["ctrl"][0].reshape(2, 6), c["P"], rtol=1e-14, atol=1e-14)
+            assert r["tca"][0] == pytest.approx(c["tca"], rel=1e-14)
+            n_ctrl += 1
+        else:
+            assert np.isnan(r["ctrl"][0]).all()
+    assert n_ctrl > 100
