@@ -279,6 +279,7 @@ def main_gpu(args, rank, local_rank, world):
                 "unit": "TFLOP/s", "frac": achieved / peak_tflops, "traffic": _ncu_traffic(rounds_mode),
                 "launches_per_step": n_k_launches, "avg_launch_ms": k_ms / max(n_k_launches, 1),
                 "flop_per_launch": alg_flops / max(n_k_launches, 1),
+                "bulk": _bulk_roofline(prof, flop_eval, peak_tflops),
                 "kernel_share_of_step": k_ms / float(step_ms[-1]),
                 "solve_profile": prof,
                 "peak_source": "DFMA-chain probe measured in this run (mpcb_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
@@ -412,6 +413,18 @@ def main_gpu(args, rank, local_rank, world):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _bulk_roofline(prof, flop_eval, peak):
+    """The same roofline over the throughput-bound rounds only (more requests than the evaluation launch has lanes): the
+    step-wide figure averages in ~2 000 launches that serve a handful of slow instances at the latency floor."""
+    b = prof.get("bulk")
+    if not b or not b["rounds"] or b["eval_ms"] <= 0:
+        return None
+    fl = (b["grad_requests"] + VALUE_SHARE * b["value_requests"]) * flop_eval
+    ach = fl / (b["eval_ms"] * 1e-3) / 1e12
+    return {"rounds": b["rounds"], "eval_ms": b["eval_ms"], "trans_ms": b["trans_ms"], "achieved": ach, "frac": ach / peak,
+            "avg_launch_ms": b["eval_ms"] / b["rounds"], "evaluations_per_s": (b["grad_requests"] + b["value_requests"]) / (b["eval_ms"] * 1e-3)}
 
 
 def _ncu_traffic(rounds_mode):

@@ -261,6 +261,11 @@ int64_t mpcb_debug_timers(MpcHandle* h, long long* out4, int64_t max_warps);
  * host until the batch is done; the persistent mode is one asynchronous launch. */
 void mpcb_last_solve_profile(MpcHandle* h, double* out6);
 
+/* Bulk phase of the last round-mode solve — the rounds that carried more evaluation requests than the evaluation launch
+ * has lanes (throughput-bound; the remaining rounds serve a few slow instances at the latency floor of one evaluation):
+ * out5 = [rounds, evaluation-kernel ms, transition-kernel ms, gradient requests, psi-only requests] summed over them. */
+void mpcb_last_solve_bulk_profile(MpcHandle* h, double* out5);
+
 /* Number of kernels launched through this handle since creation (bench.py's gpu_launches). */
 int64_t mpcb_launch_count(MpcHandle* h);
 

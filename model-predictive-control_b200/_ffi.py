@@ -82,6 +82,7 @@ SIGNATURES = {
     "mpcb_fp64_peak": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "mpcb_latency_probe": (C.c_int, [C.POINTER(C.c_double)]),
     "mpcb_launch_count": (_I64, [C.c_void_p]),
+    "mpcb_last_solve_bulk_profile": (None, [C.c_void_p, C.POINTER(C.c_double)]),
     "mpcb_last_solve_profile": (None, [C.c_void_p, C.POINTER(C.c_double)]),
 }
 

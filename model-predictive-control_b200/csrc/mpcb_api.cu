@@ -40,6 +40,9 @@ struct MpcHandle {
   int last_mode = 0;
   int64_t last_rounds = 0;
   double last_eval_ms = 0.0, last_trans_ms = 0.0;
+  // bulk phase of the last round-mode solve (rounds with more requests than the evaluation launch has lanes)
+  double bulk_eval_ms = 0.0, bulk_trans_ms = 0.0, bulk_grad = 0.0, bulk_val = 0.0; int64_t bulk_rounds = 0;
+  unsigned* rs_stats = nullptr; std::vector<unsigned> rs_stats_host; std::vector<float> rs_t_ms, rs_e_ms;
   cudaEvent_t rs_ev[3 * 64] = {};                      // per-round timing events of one chunk
   // round mode (k_solve<..., true> + k_eval_requests): saved lane state, requests, lists, counters
   double* rs_d = nullptr; size_t rs_d_cap = 0;
@@ -255,7 +258,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
   cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->fin); cudaFree(h->ifail); cudaFree(h->trace); cudaFree(h->dev);
-  cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_keys); cudaFree(h->rs_counters);
+  cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_keys); cudaFree(h->rs_stats); cudaFree(h->rs_counters);
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
   if (h->pin) cudaFreeHost(h->pin);
@@ -270,6 +273,10 @@ void mpcb_last_solve_profile(MpcHandle* h, double* out) {
   if (!h || !out) return;
   out[0] = h->last_mode; out[1] = h->last_tile; out[2] = (double)h->last_rounds;
   out[3] = h->last_eval_ms; out[4] = h->last_trans_ms; out[5] = h->last_mode ? (double)h->last_rounds : 1.0;
+}
+void mpcb_last_solve_bulk_profile(MpcHandle* h, double* out) {
+  if (!h || !out) return;
+  out[0] = (double)h->bulk_rounds; out[1] = h->bulk_eval_ms; out[2] = h->bulk_trans_ms; out[3] = h->bulk_grad; out[4] = h->bulk_val;
 }
 
 int mpcb_dynamics(MpcHandle* h, int64_t B, const double* x, const double* u, const double* p, int32_t clip,
@@ -409,9 +416,10 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   //    enqueues rounds ahead of the GPU and reads the request counters every few dozen rounds to stop.
   // Tile width: spare lanes are spent on speculative line-search candidates (mpcb_solve.cuh).
   int block = 64;
-  // small batches: one asynchronous persistent launch; from a few thousand instances on the rounds win
-  // (profiles/r01_round_mode.md: 218 vs 244 ms at B = 1024, 289 vs 413 ms at B = 4096, 2.6 vs 6.9 s at B = 65536)
-  const int mode = h->mode_override >= 0 ? h->mode_override : (B >= 1024 ? 1 : 0);
+  // Round mode at every batch size (measured on a B200 with the bucketed transition launches, gpurun r02s11: B = 1
+  // 55.8 vs 73.7 ms, B = 64 164 vs 207 ms, B = 512 186 vs 205 ms, B = 1023 323 vs 326 ms, B = 65536 1.69 vs 6.9 s);
+  // MPCB_MODE=persistent selects the one-launch persistent kernel.
+  const int mode = h->mode_override >= 0 ? h->mode_override : 1;
   const int64_t lane_cap = (int64_t)h->num_sms * h->warps_per_sm * 32;
   int G = 1;
   if (mode == 1) {
@@ -540,11 +548,15 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
       CK(cudaMemsetAsync(h->dbg, 0, (size_t)(ns / 32 + 2) * 2 * sizeof(long long), st));
     }
     h->last_eval_ms = 0.0; h->last_trans_ms = 0.0;
+    constexpr int64_t kStatRounds = 16384;  // request counts of the first rounds (later ones are the tail anyway)
+    if (!h->rs_stats) CK(cudaMalloc((void**)&h->rs_stats, kStatRounds * 2 * sizeof(unsigned)));
+    h->rs_t_ms.clear(); h->rs_e_ms.clear();
     for (;;) {
       for (int i = 0; i < chunk; ++i, ++round) {
         a.round = (int)round;
         e.counters = h->rs_counters + 4 * (round & 1);
         e.key_cnt_zero = a.key_cnt + MPCB_NKEY * (round & 1);
+        e.round_stats = round < kStatRounds ? h->rs_stats + 2 * round : nullptr;
         e.trace = (trace_round >= 0 && round == trace_round) ? (long long*)h->dbg : nullptr;
         CK(cudaEventRecord(h->rs_ev[3 * i], st));
         if (k.model_id == MPCB_MODEL_PACEJKA6) {
@@ -569,6 +581,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
         CK(cudaEventElapsedTime(&t1, h->rs_ev[3 * i], h->rs_ev[3 * i + 1]));
         CK(cudaEventElapsedTime(&t2, h->rs_ev[3 * i + 1], h->rs_ev[3 * i + 2]));
         h->last_trans_ms += t1; h->last_eval_ms += t2;
+        h->rs_t_ms.push_back(t1); h->rs_e_ms.push_back(t2);
         if (log) std::fprintf(log, "%lld %u %u %.4f %.4f\n", (long long)(round - chunk + i), h->rs_counters_host[4 * i],
                               h->rs_counters_host[4 * i + 1], t1, t2);
       }
@@ -608,6 +621,18 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
                      "with a wide lane %llu, with a slow lane %llu\n", c[0], c[2], c[3], c[4], c[5], c[6], c[7]);
     }
     h->last_rounds = round;
+    {  // bulk / tail split of the profile: which rounds carried more requests than the evaluation launch has lanes
+      const int64_t nr = std::min<int64_t>(round, kStatRounds);
+      h->rs_stats_host.resize((size_t)nr * 2);
+      CK(cudaMemcpy(h->rs_stats_host.data(), h->rs_stats, (size_t)nr * 2 * sizeof(unsigned), cudaMemcpyDeviceToHost));
+      h->bulk_eval_ms = h->bulk_trans_ms = h->bulk_grad = h->bulk_val = 0.0; h->bulk_rounds = 0;
+      for (int64_t r = 0; r < nr && r < (int64_t)h->rs_e_ms.size(); ++r) {
+        const double g = h->rs_stats_host[2 * r], v = h->rs_stats_host[2 * r + 1];
+        if (g + v > (double)ens) {
+          h->bulk_eval_ms += h->rs_e_ms[r]; h->bulk_trans_ms += h->rs_t_ms[r]; h->bulk_grad += g; h->bulk_val += v; h->bulk_rounds++;
+        }
+      }
+    }
     return leave(h, st);
   }
   if (h->debug_timers) {
@@ -674,6 +699,9 @@ int mpcb_solve_host(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const do
   size_t o_obs = pk.add(has_obs ? sizeof(double) * B * k.n_obs * MPCB_OBS_DIM : 0);
   size_t o_lb = pk.add(sizeof(double) * k.n), o_ub = pk.add(sizeof(double) * k.n);
   size_t o_U = pk.add(sizeof(double) * B * k.n);
+  // multipliers travel only when D is bounded: with D = R^m (the reference's case, main.py:57) the ALM never reads or
+  // writes them, and [B, nx N] doubles each way is 2.6x the rest of the call's traffic
+  if (!k.bounded) lambda = nullptr;
   size_t o_lam = pk.add(lambda ? sizeof(double) * B * k.m : 0);
   size_t in_end = pk.off;
   size_t o_status = pk.add(sizeof(int32_t) * B), o_iters = pk.add(sizeof(int32_t) * 2 * B);

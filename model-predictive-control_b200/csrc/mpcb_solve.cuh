@@ -1128,6 +1128,7 @@ struct EvalArgs {
   unsigned* counters;       // this round's [4]
   unsigned* ctl;            // [4] control words read by the next transition launch: [0] live tiles
   int32_t* key_cnt_zero;    // [MPCB_NKEY] bucket counts the next transition launch appends to (zeroed here)
+  unsigned* round_stats;    // [2] this round's (gradient, psi-only) request counts, kept for the solve profile; or null
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
   long long* trace;         // diagnostic (MPCB_EVAL_TRACE=round): per chunk [cycles, first slot] or null
   int split_ok;             // 0: never use the split evaluation (MPCB_SPLIT=0)
@@ -1153,6 +1154,7 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const Vec scr{e.escr + eslot, e.ens};
   const unsigned ng = e.counters[0], nv = e.counters[1];
   if (blockIdx.x == 0 && threadIdx.x == 0 && e.ctl) e.ctl[0] = e.counters[3];
+  if (blockIdx.x == 0 && threadIdx.x == 0 && e.round_stats) { e.round_stats[0] = ng; e.round_stats[1] = nv; }
   if (blockIdx.x == 0 && threadIdx.x < MPCB_NKEY && e.key_cnt_zero) e.key_cnt_zero[threadIdx.x] = 0;
   const unsigned n_warps = gridDim.x * (blockDim.x >> 5);
   const unsigned cv = (nv + 31u) >> 5;

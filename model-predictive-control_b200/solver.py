@@ -110,8 +110,13 @@ class BatchedMpc:
         """dict(mode, tile, rounds, eval_ms, trans_ms, eval_launches) of the last solve (CUDA events inside the library)."""
         out = (C.c_double * 6)()
         self._lib.mpcb_last_solve_profile(self._h, out)
-        return dict(mode="rounds" if out[0] else "persistent", tile=int(out[1]), rounds=int(out[2]), eval_ms=out[3],
+        prof = dict(mode="rounds" if out[0] else "persistent", tile=int(out[1]), rounds=int(out[2]), eval_ms=out[3],
                     trans_ms=out[4], eval_launches=int(out[5]))
+        if out[0]:
+            b = (C.c_double * 5)()
+            self._lib.mpcb_last_solve_bulk_profile(self._h, b)
+            prof["bulk"] = dict(rounds=int(b[0]), eval_ms=b[1], trans_ms=b[2], grad_requests=b[3], value_requests=b[4])
+        return prof
 
     def default_solver_params(self):
         return _ffi.default_solver_params(self.N)
