@@ -218,15 +218,23 @@ void mpcb_default_car_params(double* c11);
 int mpcb_game_payoff(MpcHandle* h, int64_t B, int32_t M, const double* ego, const double* cars, const double* car_params,
                      double* payoff_out, int32_t* decision_out, double* ctrl_out, double* tca_out, void* stream);
 
+/* Bounds evidence without compute-sanitizer (closed on the B200 pool): a handle created with MPCB_GUARDS=1 in the
+ * environment puts every scratch buffer it allocates between two 4 KiB canary regions; this synchronises the device
+ * and returns the number of canary bytes that no longer hold their pattern (0 = no kernel wrote outside its buffers),
+ * -2 if the handle was created without guards, -3 on a CUDA error. */
+int64_t mpcb_check_guards(MpcHandle* h);
+
 /* Per-solve latency of the last solve on this handle (the metric's "p50 solve latency"; alpaqa reports elapsed_time per
  * solve, controller.py:60): out is a DEVICE buffer of B + 1 uint64 — the GPU's %globaltimer (ns) at which instance b
  * returned its answer, and in out[B] the time the solve started on the GPU.  B must equal the last solve's batch. */
 int mpcb_last_finish_ns(MpcHandle* h, int64_t B, uint64_t* out, void* stream);
 
 /* Per-iteration trace in place of the reference's host progress callback (controller.py:23-24,38 prints info.ψ every
- * PANOC iteration): mpcb_set_trace(h, cap) makes every later solve on the handle record psi at the top of each inner
- * iteration (all PANOC runs of the ALM loop, in order) into a handle-owned buffer [B, cap]; cap = 0 turns it off.
- * mpcb_last_trace copies it to a DEVICE buffer [B, cap]; iterations that were not reached hold NaN. */
+ * PANOC iteration): mpcb_set_trace(h, cap) makes every later solve on the handle record (psi, phi_gamma, gamma, c) — cost,
+ * forward-backward envelope, step size (fields of alpaqa's progress info) and the line-search candidate that produced the
+ * iterate (c = 0..7: tau = 2^-c, 8: the forced prox step, -1: start of a PANOC run) — at the top of each inner iteration
+ * (all PANOC runs of the ALM loop, in order) into a handle-owned buffer [B, cap, 4]; cap = 0 turns it off.
+ * mpcb_last_trace copies it to a DEVICE buffer [B, cap, 4]; iterations that were not reached hold NaN. */
 int mpcb_set_trace(MpcHandle* h, int32_t cap);
 int mpcb_last_trace(MpcHandle* h, int64_t B, double* trace_out, void* stream);
 

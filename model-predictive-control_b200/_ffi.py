@@ -72,6 +72,7 @@ SIGNATURES = {
     "mpcb_solve_host": (C.c_int, [C.c_void_p, C.POINTER(MpcSolverParams), _I64] + [_P] * 14),
     "mpcb_default_car_params": (None, [C.POINTER(C.c_double)]),
     "mpcb_game_payoff": (C.c_int, [C.c_void_p, _I64, C.c_int32, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "mpcb_check_guards": (_I64, [C.c_void_p]),
     "mpcb_last_finish_ns": (C.c_int, [C.c_void_p, _I64, _P, _P]),
     "mpcb_set_trace": (C.c_int, [C.c_void_p, C.c_int32]),
     "mpcb_last_trace": (C.c_int, [C.c_void_p, _I64, _P, _P]),

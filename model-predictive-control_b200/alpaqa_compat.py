@@ -47,8 +47,8 @@ class StructuredPANOCLBFGSProgressInfo:
     """What the reference's callback receives (controller.py:23-24 reads `.ψ`): one per inner iteration, built from
     the kernel's trace buffer after the solve."""
 
-    def __init__(self, k=0, ψ=float("nan"), instance=0):
-        self.k, self.ψ, self.instance = k, ψ, instance
+    def __init__(self, k=0, ψ=float("nan"), φγ=float("nan"), γ=float("nan"), instance=0):
+        self.k, self.ψ, self.φγ, self.γ, self.instance = k, ψ, φγ, γ, instance
 
 
 class Box:
@@ -205,8 +205,8 @@ class ALMSolver:
         if cb is not None:
             tr = mpc.last_trace(1)[0].cpu().numpy()
             for k, v in enumerate(tr[:int(st.inner_iterations[0]) + int(st.outer_iterations[0])]):
-                if v == v:
-                    cb(StructuredPANOCLBFGSProgressInfo(k=k, ψ=float(v), instance=0))
+                if v[0] == v[0]:
+                    cb(StructuredPANOCLBFGSProgressInfo(k=k, ψ=float(v[0]), φγ=float(v[1]), γ=float(v[2]), instance=0))
         elapsed = timedelta(seconds=time.perf_counter() - t0)
         status = [SolverStatus(int(s)) for s in st.status]
         extra = {"hessian_step_size_heuristic": "off (ignored)", "road_layout": {0: "shared", 1: "table", 2: "per_instance"}[mpc.desc.road_mode]}

@@ -33,6 +33,11 @@ struct MpcHandle {
   int tile_override = 0;                               // MPCB_TILE env: force the lanes-per-instance width
   int last_tile = 0;
   int mode_override = -1;                              // MPCB_MODE env: 0 persistent kernel, 1 rounds
+  // MPCB_GUARDS=1: every grow-only scratch buffer sits between two 4 KiB canary regions (0xA5); mpcb_check_guards counts
+  // the canary bytes that changed.  (compute-sanitizer is closed on the B200 pool: this is the bounds evidence.)
+  int guards = 0;
+  struct GuardedAlloc { void* user; void* base; size_t bytes; };
+  std::vector<GuardedAlloc> guarded;
   int spec_w = 0;                                      // MPCB_SPECW env: fixed speculation window (0 = device policy)
   int spec_live_wide = 4096, spec_live_mid = 12288;    // MPCB_SPEC_LIVE="wide,mid": live-tile thresholds of the policy
   int split_ok = 1;                                    // MPCB_SPLIT env (0: never use the split evaluation)
@@ -83,12 +88,36 @@ int cuda_fail(MpcHandle* h, cudaError_t e, const char* where) {
     if (e__ != cudaSuccess) return cuda_fail(h, e__, #call);      \
   } while (0)
 
+constexpr size_t kGuardBytes = 4096;
+
+// cudaFree of a scratch buffer of the handle (its allocation starts kGuardBytes earlier when it is guarded).
+void free_scratch(MpcHandle* h, void* user) {
+  if (!user) return;
+  for (size_t i = 0; i < h->guarded.size(); ++i)
+    if (h->guarded[i].user == user) {
+      cudaFree(h->guarded[i].base);
+      h->guarded.erase(h->guarded.begin() + (long)i);
+      return;
+    }
+  cudaFree(user);
+}
+
 template <class T>
 int grow(MpcHandle* h, T** ptr, size_t* cap, size_t need_bytes, cudaStream_t st) {
   if (need_bytes <= *cap) return 0;
-  if (*ptr) { CK(cudaStreamSynchronize(st)); CK(cudaFree(*ptr)); *ptr = nullptr; *cap = 0; }
+  if (*ptr) { CK(cudaStreamSynchronize(st)); free_scratch(h, *ptr); *ptr = nullptr; *cap = 0; }
   size_t sz = need_bytes + need_bytes / 8;
-  CK(cudaMalloc((void**)ptr, sz));
+  if (!h->guards) {
+    CK(cudaMalloc((void**)ptr, sz));
+  } else {
+    sz = (sz + 255) & ~size_t(255);
+    char* base = nullptr;
+    CK(cudaMalloc((void**)&base, sz + 2 * kGuardBytes));
+    CK(cudaMemsetAsync(base, 0xA5, kGuardBytes, st));
+    CK(cudaMemsetAsync(base + kGuardBytes + sz, 0xA5, kGuardBytes, st));
+    *ptr = (T*)(base + kGuardBytes);
+    h->guarded.push_back({(void*)*ptr, (void*)base, sz});
+  }
   *cap = sz;
   return 0;
 }
@@ -243,6 +272,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
     int g = std::atoi(e);
     if (g == 1 || g == 8) h->tile_override = g;
   }
+  if (const char* e = std::getenv("MPCB_GUARDS")) h->guards = std::atoi(e) != 0;
   if (const char* e = std::getenv("MPCB_EXACT")) { if (std::atoi(e) != 0) h->kd.exact = 1; }
   if (const char* e = std::getenv("MPCB_SPECW")) { int w = std::atoi(e); if (w >= 1 && w <= 7) h->spec_w = w; }
   if (const char* e = std::getenv("MPCB_SPEC_LIVE")) {
@@ -257,8 +287,11 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
 
 void mpcb_destroy(MpcHandle* h) {
   if (!h) return;
-  cudaFree(h->road_t); cudaFree(h->ws); cudaFree(h->wst); cudaFree(h->dbg); cudaFree(h->queue); cudaFree(h->zero_lam); cudaFree(h->gam); cudaFree(h->fin); cudaFree(h->ifail); cudaFree(h->trace); cudaFree(h->dev);
-  cudaFree(h->rs_d); cudaFree(h->rs_i); cudaFree(h->rs_req); cudaFree(h->rs_escr); cudaFree(h->rs_keys); cudaFree(h->rs_stats); cudaFree(h->rs_counters);
+  for (void* q : {(void*)h->road_t, (void*)h->ws, (void*)h->wst, (void*)h->dbg, (void*)h->zero_lam, (void*)h->gam, (void*)h->fin,
+                  (void*)h->ifail, (void*)h->trace, (void*)h->dev, (void*)h->rs_d, (void*)h->rs_i, (void*)h->rs_req,
+                  (void*)h->rs_escr, (void*)h->rs_keys})
+    free_scratch(h, q);
+  cudaFree(h->queue); cudaFree(h->rs_stats); cudaFree(h->rs_counters);
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
   if (h->pin) cudaFreeHost(h->pin);
@@ -462,7 +495,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   CK(cudaMemsetAsync(h->fin, 0xFF, (size_t)(B + 1) * sizeof(unsigned long long), st));
   h->trace_B = 0;
   if (h->trace_cap > 0) {
-    const size_t tb = (size_t)B * h->trace_cap * sizeof(double);
+    const size_t tb = (size_t)B * h->trace_cap * 4 * sizeof(double);
     if ((rc = grow(h, &h->trace, &h->trace_buf_cap, tb, st))) return rc;
     CK(cudaMemsetAsync(h->trace, 0xFF, tb, st));  // NaN = iteration not reached
     h->trace_B = B;
@@ -781,6 +814,22 @@ int mpcb_game_payoff(MpcHandle* h, int64_t B, int32_t M, const double* ego, cons
   return MPCB_OK;
 }
 
+int64_t mpcb_check_guards(MpcHandle* h) {
+  if (!h) return -1;
+  if (!h->guards) return -2;  // created without MPCB_GUARDS=1
+  if (cudaDeviceSynchronize() != cudaSuccess) return -3;
+  std::vector<unsigned char> buf(kGuardBytes);
+  int64_t bad = 0;
+  for (const auto& g : h->guarded) {
+    for (int side = 0; side < 2; ++side) {
+      const char* src = (const char*)g.base + (side ? kGuardBytes + g.bytes : 0);
+      if (cudaMemcpy(buf.data(), src, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) return -3;
+      for (unsigned char c : buf) bad += c != 0xA5;
+    }
+  }
+  return bad;
+}
+
 int mpcb_last_finish_ns(MpcHandle* h, int64_t B, uint64_t* out, void* stream) {
   if (!h || !out || B < 0) return fail(h, MPCB_E_ARG, "mpcb_last_finish_ns: bad argument");
   if (B != h->gam_B || !h->fin) return fail(h, MPCB_E_ARG, "mpcb_last_finish_ns: B must be the batch of the last solve on this handle");
@@ -804,7 +853,7 @@ int mpcb_last_trace(MpcHandle* h, int64_t B, double* trace_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   if ((rc = enter(h, st))) return rc;
-  CK(cudaMemcpyAsync(trace_out, h->trace, (size_t)B * h->trace_cap * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(trace_out, h->trace, (size_t)B * h->trace_cap * 4 * sizeof(double), cudaMemcpyDeviceToDevice, st));
   return leave(h, st);
 }
 

@@ -46,7 +46,7 @@ struct SolveArgs {
   double *psi, *res;
   unsigned long long* fin_ns;  // optional [B + 1]: %globaltimer (ns) when instance b finished; [B] = start of the solve
   int32_t* ifail_out;  // [B] PANOC runs of the ALM loop that did not converge (alpaqa stats: inner_convergence_failures)
-  double* trace;       // optional [B, trace_cap]: psi at the top of every inner iteration (the progress callback's info.ψ)
+  double* trace;       // optional [B, trace_cap, 4]: (psi, phi_gamma, gamma, accepted candidate) at the top of every inner iteration (the progress callback's info)
   int trace_cap;
   double* gam_out;  // [B] final step size gamma of every instance's last PANOC run (alpaqa's inner stats: final γ)
   double* ws;    // per-lane rows   [LaneMap.total, ns]
@@ -77,7 +77,7 @@ struct SolveArgs {
   int spec_live_wide, spec_live_mid;  // live tiles up to which the window is G-1 wide / 3 wide (1 beyond)
   const unsigned* ctl;       // [4] device control words: [0] live tiles of the previous round
 };
-constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 27;
+constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 28;
 constexpr int MPCB_NKEY = 16;       // transition buckets: one per SolveState, ST_LS_STEP split by phase
 constexpr int MPCB_ROUND_BLOCK = 128;  // lanes per CTA of a transition launch
 
@@ -109,8 +109,11 @@ struct TileMap {
   }
 };
 
+#ifndef MPCB_T_MINB
+#define MPCB_T_MINB 1  // min resident CTAs per SM asked of the transition launch (register cap); A/B with -DMPCB_T_MINB=n
+#endif
 template <int MODEL, int G, bool ROUND>
-__global__ void __launch_bounds__(ROUND ? MPCB_ROUND_BLOCK : 64)
+__global__ void __launch_bounds__(ROUND ? MPCB_ROUND_BLOCK : 64, ROUND ? MPCB_T_MINB : 1)
 k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   constexpr int NX = Fm<MODEL>::NX;
   constexpr int K = ROUND ? 0 : fm_stage_doubles<MODEL>();  // round mode: the stage Jacobians live in the evaluation kernel's scratch
@@ -138,9 +141,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       int64_t g = tile_sel, start = 0;
       int key = -1;
       int64_t off = 0;
-#pragma unroll 1
+      int kcv[MPCB_NKEY];  // all counts requested at once (16 dependent L2 round trips otherwise, in every launch)
+#pragma unroll
+      for (int kq = 0; kq < MPCB_NKEY; ++kq) kcv[kq] = kc[kq];
+#pragma unroll
       for (int kq = 0; kq < MPCB_NKEY; ++kq) {
-        const int64_t c = kc[kq];
+        const int64_t c = kcv[kq];
         const int64_t cp = (c + TPW - 1) / TPW * TPW;
         if (key < 0 && g < start + cp) { key = kq; off = g - start; if (off >= c) key = MPCB_NKEY; }
         start += cp;
@@ -224,6 +230,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   double psi = 0, psi_hat = 0, gTp = 0, pTp = 0, L = 0, gam = 0, phi = 0, tau0 = 0, sigma = 0, hfd = 0, hh = 0;
   double eps_tol = 0, peps = 0, ppsi = 0, norm_e2 = 0;
   int alm_i = 0, inner_total = 0, pstatus = 0, n_ifail = 0;
+  int last_c = -1;  // line-search candidate that produced the current iterate: 0..7 -> tau = 2^-c, 8 = the prox step, -1 = start of a run
   unsigned long long mask0 = 0, mask1 = 0;  // inactive-set bitmask (n <= 128)
   auto mbit = [&](int j) { return j < 64 ? (mask0 >> j) & 1ull : (mask1 >> (j - 64)) & 1ull; };
   // ---- per-lane registers (this lane's candidate / evaluation request) ----
@@ -239,7 +246,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
 #define MPCB_STATE_D(X) X(psi) X(psi_hat) X(gTp) X(pTp) X(L) X(gam) X(phi) X(tau0) X(sigma) X(hfd) X(hh) X(eps_tol) X(peps) \
   X(ppsi) X(norm_e2) X(psi_n) X(psi_hat_n) X(gTp_n) X(pTp_n) X(L_n) X(gam_n) X(phi_n)
 #define MPCB_STATE_I(X) X(state) X(cl) X(cb) X(fd_lane) X(ge_row) X(ge_lane) X(k) X(no_prog) X(lb_idx) X(lb_full) X(hb) X(lsw) \
-  X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for) X(lsW) X(n_ifail)
+  X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for) X(lsW) X(n_ifail) X(last_c)
   bool dead = notile;  // round mode: this group has no tile / its tile has no instance left
   if constexpr (ROUND) {
     if (a.round > 0 && !notile) {
@@ -635,7 +642,10 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         phi = psi + pTp / (2.0 * gam) + gTp;
         state = ST_ITER_TOP;
       } else if (state == ST_ITER_TOP) {
-        if (a.trace && l == 0 && inner_total + k < a.trace_cap) a.trace[b * a.trace_cap + inner_total + k] = psi;
+        if (a.trace && l == 0 && inner_total + k < a.trace_cap) {  // (psi, FBE phi_gamma, gamma, accepted candidate) of iterate k
+          double* tr = a.trace + ((int64_t)b * a.trace_cap + inner_total + k) * 4;
+          tr[0] = psi; tr[1] = phi; tr[2] = gam; tr[3] = (double)(k == 0 ? -1 : last_c);
+        }
         double eps_k = sqrt(pTp);
         int stop = 0;
         if (!isfinite(eps_k)) stop = MPCB_STATUS_NOT_FINITE;
@@ -924,6 +934,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
             printf("[trace] outer %d k %d rounds %d accepted c=%d lane %d window %d gamma %s fd_ready %d pTp %.3e\n", alm_i, k,
                    t_rounds, cw, jw, lsw, gw == gam ? "same" : "halved", (int)fd_ready, pw);
         }
+        last_c = __shfl_sync(tmask, c_idx, tbase + jw);
         psi = tbcast(psi_n, jw); psi_hat = tbcast(psi_hat_n, jw);
         gTp = tbcast(gTp_n, jw); pTp = tbcast(pTp_n, jw);
         L = tbcast(L_n, jw); gam = tbcast(gam_n, jw);

@@ -318,6 +318,10 @@ class BatchedMpc:
                    self._h, "mpcb_game_payoff")
         return payoff, decision, ctrl, tca
 
+    def check_guards(self):
+        """Canary bytes around the handle's scratch buffers that were overwritten (handle created under MPCB_GUARDS=1)."""
+        return int(self._lib.mpcb_check_guards(self._h))
+
     def last_solve_latency_ms(self, B):
         """[B] milliseconds from the start of the last solve on the GPU to the moment each instance returned its answer
         (GPU %globaltimer stamps written by the kernels)."""
@@ -333,9 +337,9 @@ class BatchedMpc:
         self._trace_cap = int(cap)
 
     def last_trace(self, B):
-        """[B, cap] psi per inner iteration of the last solve (NaN where an instance had already stopped)."""
+        """[B, cap, 4] (psi, phi_gamma, gamma, accepted candidate) per inner iteration of the last solve (NaN = not reached)."""
         cap = getattr(self, "_trace_cap", 0)
-        out = torch.empty(B, cap, dtype=torch.float64, device=self.device)
+        out = torch.empty(B, cap, 4, dtype=torch.float64, device=self.device)
         with torch.cuda.device(self.device):
             _ffi.check(self._lib.mpcb_last_trace(self._h, B, _dev_ptr(out, torch.float64, "trace"), self._stream()),
                        self._h, "mpcb_last_trace")

@@ -224,3 +224,42 @@ def test_gpu_vs_oracle_no_worse_than_oracle_vs_oracle(mp, orc, N, B):
     assert np.mean(e_go < 1e-5) >= np.mean(e_oo < 1e-5) - 0.15
     assert same_go >= same_oo - 0.15
     assert (st.status.cpu().numpy() == 1).all() and (a["status"] == 1).all()
+
+
+# ------------------------------------------------------------------ 4. bounds and race evidence without compute-sanitizer
+@pytest.mark.parametrize("mode", ["rounds", "persistent"])
+def test_guard_canaries_and_repeat_determinism(mp, mode, monkeypatch):
+    """compute-sanitizer is closed on the B200 pool (its runs left GPUs needing a reset), so: (a) every scratch buffer of
+    a handle created under MPCB_GUARDS=1 sits between canary regions that must still hold their pattern after solves of
+    every kind (no kernel writes outside its buffers); (b) five runs of the same batch, interleaved with other work on
+    the handle, return identical bits — tiles share workspace rows and publish results to each other through global
+    memory behind tile barriers, so a missing barrier or a racy read would show up as run-to-run differences."""
+    import torch
+    from mpcb200 import workloads as wl
+    monkeypatch.setenv("MPCB_GUARDS", "1")
+    monkeypatch.setenv("MPCB_MODE", mode)
+    N, B = 20, 777   # ragged
+    w = wl.tracking_batch(B, N, 100, seed=99)
+    prob = mp.BatchedMpc(N=N, S=100, road_mode=mp.ROAD_TABLE, n_roads=2)
+    outs = []
+    for rep in range(5):
+        U, _, st = prob.solve(w["x0"], w["road"], w["U0"].copy(), road_idx=w["road_idx"])
+        outs.append((U.clone(), st.status.clone(), st.inner_iterations.clone(), st.psi.clone()))
+        # other shapes through the same handle in between: smaller batch (stale workspace contents), evaluation calls
+        prob.solve(w["x0"][:100 + rep], w["road"], w["U0"][:100 + rep].copy(), road_idx=w["road_idx"][:100 + rep])
+        prob.value_grad(w["x0"], w["U0"], w["road"], road_idx=w["road_idx"])
+        prob.rollout(w["x0"], w["U0"], w["road"], road_idx=w["road_idx"])
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert torch.equal(a, b)
+    assert prob.check_guards() == 0
+    # the other problem families on guarded handles
+    bd = mp.BatchedMpc(N=12, S=100, road_mode=mp.ROAD_TABLE, n_roads=2, flags=mp.FLAG_BOUNDED_D, D_lower=[-np.inf] * 6,
+                       D_upper=[np.inf, np.inf, np.inf, -1.0, np.inf, np.inf])
+    w12 = wl.tracking_batch(200, 12, 100, seed=31)
+    bd.solve(w12["x0"], w12["road"], w12["U0"].copy(), lam=np.zeros((200, 72)), road_idx=w12["road_idx"])
+    assert bd.check_guards() == 0
+    lc = wl.lane_change_batch(300, 40, 100, seed=5, n_obs=2)
+    kin = mp.BatchedMpc(N=40, S=100, model_id=1, road_mode=mp.ROAD_BEZIER, flags=mp.FLAG_LANE | mp.FLAG_OBST, n_obs=2, v_ref=20.0)
+    kin.solve(lc["x0"], lc["ctrl"], lc["U0"].copy(), obs=lc["obs"])
+    assert kin.check_guards() == 0

@@ -18,7 +18,7 @@ def main():
     w = wl.tracking_batch(B, N, 100, seed=2)
     x0, road = torch.tensor(w["x0"], device=dev), torch.tensor(w["road"], device=dev)
     ridx, U0 = torch.tensor(w["road_idx"], device=dev), torch.tensor(w["U0"], device=dev)
-    for i in range(2):
+    for i in range(int(os.environ.get("PROF_REPS", "2"))):
         U = U0.clone()
         torch.cuda.synchronize()
         t = time.perf_counter()
