@@ -41,6 +41,7 @@ struct MpcHandle {
   int spec_w = 0;                                      // MPCB_SPECW env: fixed speculation window (0 = device policy)
   int spec_live_wide = 4096, spec_live_mid = 12288;    // MPCB_SPEC_LIVE="wide,mid": live-tile thresholds of the policy
   int split_ok = 1;                                    // MPCB_SPLIT env (0: never use the split evaluation)
+  int pit_ok = 1;                                      // MPCB_PIT env (0: never use the parallel-in-time evaluation)
   long long eval_trace_round = -1;                     // MPCB_EVAL_TRACE env
   int last_mode = 0;
   int64_t last_rounds = 0;
@@ -280,6 +281,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
     if (std::sscanf(e, "%d,%d", &a, &b) == 2 && a >= 0 && b >= a) { h->spec_live_wide = a; h->spec_live_mid = b; }
   }
   if (const char* e = std::getenv("MPCB_SPLIT")) h->split_ok = std::atoi(e) != 0;
+  if (const char* e = std::getenv("MPCB_PIT")) h->pit_ok = std::atoi(e) != 0;
   if (const char* e = std::getenv("MPCB_EVAL_TRACE")) h->eval_trace_round = std::atoll(e);
   *out = h;
   return MPCB_OK;
@@ -513,9 +515,15 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   h->last_mode = mode;
   if (mode == 1) {
     // evaluation launch: one CTA of 256 lanes (255 registers each) per SM, never more lanes than requests can exist
-    int64_t eblocks = (ns + 31) / 32;   // one warp per SM sub-partition before any doubling up
-    if (eblocks > (int64_t)h->num_sms) eblocks = (int64_t)h->num_sms;
-    const int64_t ens = eblocks * 256;
+    int64_t wblocks = (ns + 31) / 32;   // CTAs with evaluation scratch: one warp per SM sub-partition before any doubling up
+    if (wblocks > (int64_t)h->num_sms) wblocks = (int64_t)h->num_sms;
+    const int64_t ens = wblocks * 256;
+    // the grid always covers every SM: CTAs beyond `wblocks` only take parallel-in-time requests (shared memory only)
+    const int64_t eblocks = h->num_sms;
+    const size_t pit_smem = sizeof(double) * (size_t)(k.model_id == MPCB_MODEL_PACEJKA6 ? fm_pit_doubles<MPCB_MODEL_PACEJKA6>(k.N)
+                                                                                         : fm_pit_doubles<MPCB_MODEL_KINEMATIC4>(k.N));
+    const size_t eval_smem = road_smem + pit_smem;
+    if (eval_smem > 200 * 1024) return fail(h, MPCB_E_UNSUPPORTED, "mpcb_solve: road table + evaluation buffers exceed shared memory");
     if ((rc = grow(h, &h->rs_d, &h->rs_d_cap, (size_t)MPCB_SD_ROWS * ns * sizeof(double), st))) return rc;
     if ((rc = grow(h, &h->rs_i, &h->rs_i_cap, (size_t)MPCB_SI_ROWS * ns * sizeof(int32_t), st))) return rc;
     // requests: want[ns] i32, list_grad[ns] i32, list_val[ns] i32, (pad) b[ns] i64, p[ns], g[ns] ptr, val[ns] f64
@@ -546,7 +554,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     e.x0 = x0; e.p = p; e.obs = obs; e.lam = lambda; e.sig_base = h->wst + (size_t)TM.SIG * nt; e.ra = ra;
     e.req_want = a.req_want; e.req_b = a.req_b; e.req_p = a.req_p; e.req_g = a.req_g; e.req_val = a.req_val;
     e.list_grad = a.list_grad; e.list_val = a.list_val; e.escr = h->rs_escr; e.ctl = h->rs_counters + 8;
-    e.split_ok = h->split_ok;
+    e.split_ok = h->split_ok; e.pit_ok = h->pit_ok; e.work_blocks = (int)wblocks;
 #define MPCB_LAUNCH_T(MODEL, GG)                                                               \
   do {                                                                                         \
     if (round == 0 && (rc = set_smem(h, k_solve<MODEL, GG, true>, box_smem))) return rc;       \
@@ -557,8 +565,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     case 8: MPCB_LAUNCH_T(MODEL, 8); break;                                                    \
     default: MPCB_LAUNCH_T(MODEL, 1); break;                                                   \
   }
-    if (k.model_id == MPCB_MODEL_PACEJKA6) { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_PACEJKA6>, road_smem))) return rc; }
-    else { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_KINEMATIC4>, road_smem))) return rc; }
+    if (k.model_id == MPCB_MODEL_PACEJKA6) { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_PACEJKA6>, eval_smem))) return rc; }
+    else { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_KINEMATIC4>, eval_smem))) return rc; }
     int64_t round = 0;
     // no instance can need more: <= ~40 rounds per PANOC iteration (9 trials x descent-lemma steps) over at most
     // max_iter iterations per PANOC run and ~8 runs of the tolerance continuation; a guard against a hang, not a limit
@@ -595,11 +603,11 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
         if (k.model_id == MPCB_MODEL_PACEJKA6) {
           MPCB_LAUNCH_T_G(MPCB_MODEL_PACEJKA6)
           CK(cudaEventRecord(h->rs_ev[3 * i + 1], st));
-          k_eval_requests<MPCB_MODEL_PACEJKA6><<<(unsigned)eblocks, 256, road_smem, st>>>(k, e);
+          k_eval_requests<MPCB_MODEL_PACEJKA6><<<(unsigned)eblocks, 256, eval_smem, st>>>(k, e);
         } else {
           MPCB_LAUNCH_T_G(MPCB_MODEL_KINEMATIC4)
           CK(cudaEventRecord(h->rs_ev[3 * i + 1], st));
-          k_eval_requests<MPCB_MODEL_KINEMATIC4><<<(unsigned)eblocks, 256, road_smem, st>>>(k, e);
+          k_eval_requests<MPCB_MODEL_KINEMATIC4><<<(unsigned)eblocks, 256, eval_smem, st>>>(k, e);
         }
         CK(cudaEventRecord(h->rs_ev[3 * i + 2], st));
         if (log || i == chunk - 1)

@@ -38,14 +38,18 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
                               double a_r, double zf, double zr, double stf, double ctf, double str_, double ctr,
                               double sgn, double* kp, double* kq, Lin& L) {
     const double vx = q[1], vy = q[2], w = q[3];
-    const double frx = (v.cm1 - v.cm2 * vx) * su.d - v.cr0 * sgn - v.cr2 * vx * vx;
+    // Every multiply-add of the primal is spelled out: left to the compiler, `frx - ffy * sdl` is fused into an FMA in
+    // one instantiation and built from the product `ffy * sdl` that the linearisation shares in another, and the state
+    // bits would depend on whether (and how) the caller uses L (round 2: the primal-only stage of the parallel-in-time
+    // evaluation must reproduce the gradient variants' states bit for bit).
+    const double frx = fma(-(v.cr2 * vx), vx, fma(fma(-v.cm2, vx, v.cm1), su.d, -(v.cr0 * sgn)));
     const double ffy = v.df * stf, fry = v.dr * str_;
-    kp[0] = vx * c - vy * s;
-    kp[1] = vx * s + vy * c;
+    kp[0] = fma(vx, c, -(vy * s));
+    kp[1] = fma(vx, s, vy * c);
     kq[0] = w;
-    kq[1] = (frx - ffy * su.sdl + v.m * vy * w) * v.inv_m;
-    kq[2] = (fry + ffy * su.cdl - v.m * vx * w) * v.inv_m;
-    kq[3] = (ffy * v.lf * su.cdl - fry * v.lr) * v.inv_iz;
+    kq[1] = fma(v.m * vy, w, fma(-ffy, su.sdl, frx)) * v.inv_m;
+    kq[2] = fma(-(v.m * vx), w, fma(ffy, su.cdl, fry)) * v.inv_m;
+    kq[3] = fma(ffy * v.lf, su.cdl, -(fry * v.lr)) * v.inv_iz;
     if (GRAD) {
       L.s = s; L.c = c; L.f0 = kp[0]; L.f1 = kp[1];
       const double Gf = v.df * ctf * v.cf * v.bf * fm_rcp(fma(zf, zf, 1.0));
@@ -245,8 +249,8 @@ template <> struct Fm<MPCB_MODEL_KINEMATIC4> {
     fm_sincos(q[0] + su.beta, &s, &c);
     kp[0] = q[1] * c;
     kp[1] = q[1] * s;
-    kq[0] = q[1] * su.sb * v.inv_lr;
-    kq[1] = v.acc * su.d - v.mu * q[1];
+    kq[0] = (q[1] * su.sb) * v.inv_lr;
+    kq[1] = fma(v.acc, su.d, -(v.mu * q[1]));  // explicit, as in the Pacejka model: the same bits in every instantiation
     if (GRAD) {
       L.s = s; L.c = c; L.v = q[1]; L.sb_lr = su.sb * v.inv_lr; L.cb_lr_db = su.cb * v.inv_lr * su.dbeta;
       L.db = su.dbeta; L.acc = v.acc; L.mu = v.mu;
@@ -631,6 +635,175 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
     for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
   }
   return cost;
+}
+
+// Primal-only stage with the GRADIENT variant's arithmetic: the model call is Fm::call<true> (its sincos kernels, not the
+// value-only variant's shorter sin kernel, whose last bits differ), inlined with the linearisation unused, so the
+// compiler drops the Lin computation and every tangent: the state bits are those of stage_fm / stage_fm_split at about
+// the value-only call's latency.  Phase 1 of the parallel-in-time evaluation.
+template <int MODEL>
+MPCB_DEV void rk4_fm_primal(double* p, double* q, const StageU& su, const VehP& v, double h) {
+  using M = Fm<MODEL>;
+  constexpr int NQ = M::NQ;
+  const double h6 = h * (1.0 / 6.0);
+  double kp[2] = {0.0, 0.0}, kq[NQ], accp[2] = {0.0, 0.0}, accq[NQ];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) { kq[i] = 0.0; accq[i] = 0.0; }
+#pragma unroll 1
+  for (int s = 0; s < 4; ++s) {
+    const double a = s == 0 ? 0.0 : (s == 3 ? h : 0.5 * h);
+    const double bw = (s == 0 || s == 3) ? 1.0 : 2.0;
+    double sq[NQ];
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) sq[i] = fma(a, kq[i], q[i]);
+    typename M::Lin L;
+    M::template call<true>(sq, su, v, kp, kq, L);
+    accp[0] = fma(bw, kp[0], accp[0]);
+    accp[1] = fma(bw, kp[1], accp[1]);
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) accq[i] = fma(bw, kq[i], accq[i]);
+  }
+  p[0] = fma(h6, accp[0], p[0]);
+  p[1] = fma(h6, accp[1], p[1]);
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) q[i] = fma(h6, accq[i], q[i]);
+}
+
+template <int MODEL>
+__device__ __noinline__ void stage_fm_primal(double* pq, double ud, double udl) {
+  using M = Fm<MODEL>;
+  constexpr int NQ = M::NQ;
+  const VehP& v = s_veh;
+  StageU su;
+  make_stage_u<MODEL>(su, ud, udl, v, true);
+  double p[2] = {pq[0], pq[1]}, q[NQ];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) q[i] = pq[2 + i];
+  const int n_sub = s_desc.n_sub;
+  const double h = s_desc.h;
+#pragma unroll 1
+  for (int e = 0; e < n_sub; ++e) rk4_fm_primal<MODEL>(p, q, su, v, h);
+  pq[0] = p[0]; pq[1] = p[1];
+#pragma unroll
+  for (int i = 0; i < NQ; ++i) pq[2 + i] = q[i];
+}
+
+// ---- parallel-in-time evaluation: one CTA per gradient request -----------------------------------------
+// Only the PRIMAL rollout is sequential.  The stage Jacobian T_n (and the stage cost and its gradient) depends on the
+// stage's start state s_n and input u_n alone — not on earlier tangents; the tangents only meet in the horizon adjoint.
+// When few gradient requests are left (the last rounds of every batch, a lone vehicle's tick) a whole CTA takes one:
+//   phase 1  one thread rolls the primal out, s_0 .. s_N to shared memory              (16 N dependent model calls)
+//   phase 2  every stage at once: group g = stage, lane J < ND = tangent direction J of that stage from s_n,
+//            lane J = ND = cost and cost gradient of the stage at s_{n+1}               (16 dependent model calls)
+//   phase 3  one thread sums the stage costs in order and runs the N-step adjoint over shared memory.
+// The stage arithmetic is that of the split evaluation (stage_fm_primal / stage_fm_split / stage_cost: the same model
+// call on the same operands), and the sums run in the same order: psi and the gradient are bit for bit those of eval_fm_split / eval_fm
+// (tests/test_gpu_exactness.py).  Latency of one request: 0.33 -> 0.17 ms; no HBM scratch at all.
+// Shared memory (doubles): (N + 1) NX states, 2 N inputs, N K stage rows, N stage costs, 2 flags.
+template <int MODEL>
+__host__ __device__ constexpr int fm_pit_doubles(int N) {
+  return (N + 1) * Fm<MODEL>::NX + 2 * N + N * fm_stage_doubles<MODEL>() + N + 2;
+}
+
+// Called by every thread of the CTA; returns psi on every thread (NaN for a cut request).  `grad` is the request's
+// gradient row (global, strided).
+template <int MODEL>
+__device__ __noinline__ double eval_fm_pit(RoadView r, Extras ex, const double* x0, Vec U, Vec grad, double* sm, bool cut) {
+  const KDesc& d = s_desc;
+  using M = Fm<MODEL>;
+  constexpr int NX = M::NX, ND = M::ND, K = fm_stage_doubles<MODEL>();
+  const int N = d.N;
+  double* S = sm;                    // [(N + 1), NX]
+  double* UU = S + (N + 1) * NX;     // [2 N]
+  double* Jb = UU + 2 * N;           // [N, K]
+  double* Lc = Jb + N * K;           // [N]
+  double* flag = Lc + N;             // [0] dead, [1] psi
+  for (int i = threadIdx.x; i < 2 * N; i += blockDim.x) UU[i] = U(i);
+  if (threadIdx.x < NX) S[threadIdx.x] = x0[threadIdx.x];
+  if (threadIdx.x == 0) flag[0] = 0.0;
+  __syncthreads();
+  // ---- phase 1: the primal, sequential
+  if (threadIdx.x == 0) {
+    double y[NX];
+#pragma unroll
+    for (int i = 0; i < NX; ++i) y[i] = S[i];
+#pragma unroll 1
+    for (int n = 0; n < N; ++n) {
+      stage_fm_primal<MODEL>(y, UU[2 * n], UU[2 * n + 1]);
+      bool sane = true;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) sane = sane && y[i] == y[i];
+      sane = sane && fabs(y[3]) < 1.3e154 && (MODEL == MPCB_MODEL_KINEMATIC4 || fabs(y[NX == 6 ? 4 : 3]) < 1.3e154);
+      if (!sane && cut) { flag[0] = 1.0; break; }
+#pragma unroll
+      for (int i = 0; i < NX; ++i) S[(n + 1) * NX + i] = y[i];
+    }
+  }
+  __syncthreads();
+  const bool dead = flag[0] != 0.0;
+  // ---- phase 2: every stage at once
+  if (!dead) {
+    const int J = threadIdx.x & 7;
+    for (int n = threadIdx.x >> 3; n < N; n += blockDim.x >> 3) {
+      const double ud = UU[2 * n], udl = UU[2 * n + 1];
+      if (J < ND) {
+        double y[NX];
+#pragma unroll
+        for (int i = 0; i < NX; ++i) y[i] = S[n * NX + i];
+        stage_fm_split<MODEL>(y, ud, udl, Vec{Jb, 1}, n * K, J);
+      } else if (J == ND) {
+        double y[NX], gy[NX], gu[2];
+#pragma unroll
+        for (int i = 0; i < NX; ++i) y[i] = S[(n + 1) * NX + i];
+        int idx = -1;
+        Lc[n] = stage_cost<MODEL, true, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
+#pragma unroll
+        for (int i = 0; i < NX; ++i) Jb[n * K + NX * ND + 2 + i] = gy[i];
+      }
+    }
+  }
+  __syncthreads();
+  // ---- phase 3: cost sum and horizon adjoint
+  if (threadIdx.x == 0) {
+    if (dead) {
+      const double nn = nan("");
+      for (int i = 0; i < 2 * N; ++i) grad.set(i, nn);
+      flag[1] = nn;
+    } else {
+      double cost = 0.0;
+      for (int n = 0; n < N; ++n) cost += Lc[n];
+      const Vec scr{Jb, 1};
+      double lam[NX];
+#pragma unroll
+      for (int i = 0; i < NX; ++i) lam[i] = 0.0;
+#pragma unroll 1
+      for (int n = N - 1; n >= 0; --n) {
+        const int o = n * K;
+#pragma unroll
+        for (int i = 0; i < NX; ++i) lam[i] += scr(o + NX * ND + 2 + i);
+        double dots[ND];
+#pragma unroll
+        for (int j = 0; j < ND; ++j) {
+          double sacc = 0.0;
+#pragma unroll
+          for (int i = 0; i < NX; ++i) sacc = fma(scr(o + j * NX + i), lam[i], sacc);
+          dots[j] = sacc;
+        }
+        const double dx = scr(o + NX * ND), dy = scr(o + NX * ND + 1);
+        const double ud = UU[2 * n], udl = UU[2 * n + 1];
+        grad.set(2 * n, fma(2.0 * d.c[5], ud, dots[ND - 2]));
+        grad.set(2 * n + 1, fma(2.0 * d.c[4], udl, dots[ND - 1]));
+        lam[2] = lam[2] - dy * lam[0] + dx * lam[1];
+#pragma unroll
+        for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
+      }
+      flag[1] = cost;
+    }
+  }
+  __syncthreads();
+  const double psi = flag[1];
+  __syncthreads();  // the buffers are reused by the CTA's next request
+  return psi;
 }
 
 }  // namespace mpcb

@@ -1143,6 +1143,9 @@ struct EvalArgs {
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
   long long* trace;         // diagnostic (MPCB_EVAL_TRACE=round): per chunk [cycles, first slot] or null
   int split_ok;             // 0: never use the split evaluation (MPCB_SPLIT=0)
+  int pit_ok;               // 0: never use the parallel-in-time evaluation (MPCB_PIT=0)
+  int work_blocks;          // CTAs that own evaluation scratch and take chunks (the grid may be larger: CTAs beyond only take
+                            // parallel-in-time requests, which live in shared memory)
 };
 
 // Launch shape: ONE CTA of 256 lanes per SM, so a CTA's warps w and w + 4 share an SM sub-partition and
@@ -1167,18 +1170,40 @@ k_eval_requests(KDesc d, EvalArgs e) {
   if (blockIdx.x == 0 && threadIdx.x == 0 && e.ctl) e.ctl[0] = e.counters[3];
   if (blockIdx.x == 0 && threadIdx.x == 0 && e.round_stats) { e.round_stats[0] = ng; e.round_stats[1] = nv; }
   if (blockIdx.x == 0 && threadIdx.x < MPCB_NKEY && e.key_cnt_zero) e.key_cnt_zero[threadIdx.x] = 0;
-  const unsigned n_warps = gridDim.x * (blockDim.x >> 5);
   const unsigned cv = (nv + 31u) >> 5;
+  // Few gradient requests (each can have a CTA of its own next to the psi-only chunks): parallel-in-time evaluation,
+  // one request per CTA from the END of the grid (the psi-only chunks are handed out from its start).
+  const bool pit = e.pit_ok && ng > 0 && ng + (cv < 8u ? cv : 8u) <= gridDim.x;
+  if (pit) {
+    double* pit_sm = smem + (e.ra.in_smem ? e.ra.R * road_smem_doubles(d.S) : 0);
+    const unsigned ridx = gridDim.x - 1u - blockIdx.x;
+    if (ridx < ng) {
+      const int64_t slot = e.list_grad[ridx];
+      const int64_t b = e.req_b[slot];
+      const int64_t tile = slot / e.G;
+      RoadView r = road_view(e.ra, sroad, d.S, b);
+      Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
+                d.bounded ? e.sig_base + tile : nullptr, 1, e.nt};
+      const double v = eval_fm_pit<MODEL>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], e.ns}, Vec{e.req_g[slot], e.ns}, pit_sm, !d.exact);
+      if (threadIdx.x == 0) e.req_val[slot] = v;
+      return;  // (a CTA with a parallel-in-time request takes no chunks: nb below keeps them apart)
+    }
+  }
+  // CTAs that take chunks: those with evaluation scratch, minus the ones busy with parallel-in-time requests
+  unsigned nb = (unsigned)e.work_blocks < gridDim.x ? (unsigned)e.work_blocks : gridDim.x;
+  if (pit && gridDim.x - ng < nb) nb = gridDim.x - ng;
+  if (blockIdx.x >= nb) return;
+  const unsigned n_warps = nb * (blockDim.x >> 5);
   // few gradient requests (every chunk still gets a warp slot of its own on half the sub-partitions): 8 lanes per
   // request, one tangent direction each (eval_fm_split) — the latency floor of a round drops with the
   // per-warp instruction count
-  const bool split = e.split_ok && ng > 0 && ((ng + 3u) >> 2) + cv <= (n_warps >> 1);
-  const unsigned cg = split ? (ng + 3u) >> 2 : (ng + 31u) >> 5;
+  const bool split = !pit && e.split_ok && ng > 0 && ((ng + 3u) >> 2) + cv <= (n_warps >> 1);
+  const unsigned cg = pit ? 0u : (split ? (ng + 3u) >> 2 : (ng + 31u) >> 5);
   bool first = true;
   for (;;) {
     unsigned c = 0;
     if (first) {
-      c = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+      c = (threadIdx.x >> 5) * nb + blockIdx.x;
       first = false;
     } else {
       if (lane == 0) c = n_warps + atomicAdd(&e.counters[2], 1u);

@@ -263,3 +263,30 @@ def test_guard_canaries_and_repeat_determinism(mp, mode, monkeypatch):
     kin = mp.BatchedMpc(N=40, S=100, model_id=1, road_mode=mp.ROAD_BEZIER, flags=mp.FLAG_LANE | mp.FLAG_OBST, n_obs=2, v_ref=20.0)
     kin.solve(lc["x0"], lc["ctrl"], lc["U0"].copy(), obs=lc["obs"])
     assert kin.check_guards() == 0
+
+
+# ------------------------------------------------------------------ 5. the parallel-in-time evaluation of thin rounds
+@pytest.mark.parametrize("problem", ["pacejka_B4_N20", "pacejka_B40_N20", "pacejka_B2048_N12", "pacejka_bounded_B6_N12",
+                                     "kinematic_obstacles_B8_N40"])
+def test_parallel_in_time_evaluation_changes_nothing(mp, problem, monkeypatch):
+    """Thin rounds give every gradient request a CTA of its own: the primal rollout by one thread, then all stage
+    Jacobians and stage costs at once from shared memory, then the adjoint (eval_fm_pit).  Same stage arithmetic, same
+    summation orders: bit-identical to the chunked evaluations (MPCB_PIT=0) — for a lone vehicle (every round thin), for
+    batches whose tail is thin, with ALM rows, and for N = 40 (two passes over the stage groups)."""
+    monkeypatch.setenv("MPCB_MODE", "rounds")
+    out = []
+    for pit in ("0", "1"):
+        monkeypatch.setenv("MPCB_PIT", pit)
+        if problem == "pacejka_B4_N20":
+            _, _, U, _, st = _solve_tracking(mp, 20, 4, seed=8)
+        elif problem == "pacejka_B40_N20":
+            _, _, U, _, st = _solve_tracking(mp, 20, 40, seed=9)
+        elif problem == "pacejka_B2048_N12":
+            _, _, U, _, st = _solve_tracking(mp, 12, 2048, seed=10)
+        elif problem == "pacejka_bounded_B6_N12":
+            _, _, U, _, st = _solve_tracking(mp, 12, 6, seed=31, flags=mp.FLAG_BOUNDED_D, lam=True, D_lower=[-np.inf] * 6,
+                                             D_upper=[np.inf, np.inf, np.inf, -1.0, np.inf, np.inf])
+        else:
+            _, _, U, _, st = _solve_lane_change(mp, 40, 8, seed=78)
+        out.append((U, st))
+    _assert_same_solution(out[0], out[1], f"{problem}: chunked evaluations vs parallel-in-time")
