@@ -288,6 +288,31 @@ def main_gpu(args, rank, local_rank, world):
                 "hbm": {"algorithmic_bytes_per_step": alg_bytes, "achieved_gbs": alg_bytes / (k_ms * 1e-3) / 1e9,
                         "peak_gbs": _hbm_peak()}}
 
+    # ---- cross-check of the kernel durations with CUDA events: one untimed step through the host-driven loop -------
+    # (the default loop is a CUDA graph WHILE node: its per-launch durations are %globaltimer stamps written by the kernels,
+    # events cannot bracket nodes inside the loop body; MPCB_LOOP=host launches the same kernels from the host with
+    # cudaEventRecord around every launch on the launch stream)
+    os.environ["MPCB_LOOP"] = "host"
+    try:
+        prob_h = mpcb200.BatchedMpc(N=N, S=S, road_mode=mpcb200.ROAD_TABLE, n_roads=2)
+    finally:
+        os.environ.pop("MPCB_LOOP", None)
+    Uh0 = U0.clone()
+    prob_h.solve(x0, road, U0.clone(), road_idx=ridx)
+    a_ev, b_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a_ev.record()
+    prob_h.solve(x0, road, Uh0, road_idx=ridx)
+    b_ev.record()
+    torch.cuda.synchronize()
+    ph = prob_h.last_solve_profile()
+    roofline["launch_timing"] = ("graph-driven loop: per-launch durations from %globaltimer stamps at the start of each evaluation "
+                                 "launch and at the end of each round (trans_ms includes node scheduling)")
+    roofline["cuda_event_cross_check"] = {"loop": "host-driven (MPCB_LOOP=host), one untimed step", "step_ms": a_ev.elapsed_time(b_ev),
+                                          "eval_ms": ph["eval_ms"], "trans_ms": ph["trans_ms"], "rounds": ph["rounds"],
+                                          "achieved": alg_flops / (ph["eval_ms"] * 1e-3) / 1e12 if rounds_mode else None,
+                                          "bit_identical_U": bool(torch.equal(Uh0, Ubufs[W + K - 1]))}
+    del prob_h
+
     # ---- end-to-end arm: host buffers through mpcb_solve_host ---------------------------------------
     Uh = [w["U0"].copy() for _ in range(K + 1)]
     prob.solve_host(w["x0"], w["road"], Uh[K], road_idx=w["road_idx"])  # warm (allocates pinned staging)

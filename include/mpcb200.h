@@ -262,11 +262,15 @@ int mpcb_latency_probe(double* cycles8);
  * warps written (<= max_warps). */
 int64_t mpcb_debug_timers(MpcHandle* h, long long* out4, int64_t max_warps);
 
-/* Execution profile of the last mpcb_solve on this handle, measured with CUDA events on the launch stream:
- * out6 = [mode (0 persistent kernel, 1 rounds), tile width G, rounds, evaluation-kernel ms (sum over rounds),
- * transition-kernel ms (sum over rounds), evaluation launches].  mpcb_solve picks the mode (MPCB_MODE=persistent|rounds
- * overrides): in round mode the call enqueues transition + evaluation launches round after round and blocks the
- * host until the batch is done; the persistent mode is one asynchronous launch. */
+/* Execution profile of the last mpcb_solve on this handle: out6 = [mode (0 persistent kernel, 1 rounds), tile width G,
+ * rounds, evaluation-kernel ms (sum over rounds), transition-kernel ms (sum over rounds), evaluation launches].
+ * Round mode (the default; MPCB_MODE=persistent|rounds overrides) runs a transition launch and an evaluation launch per
+ * round.  The loop is driven ON THE DEVICE by a CUDA graph — WHILE(any request published) { transition; evaluation;
+ * advance } — so mpcb_solve is one asynchronous graph launch on the caller's stream, like every other call; the per-kernel
+ * times are then differences of %globaltimer stamps the kernels write (CUDA events cannot bracket the nodes of a WHILE
+ * body), and this function synchronises that stream to read them.  MPCB_LOOP=host (or a per-round diagnostic:
+ * MPCB_ROUND_LOG, MPCB_EVAL_TRACE) drives the same launches from the host instead — that call blocks the host until the
+ * batch is done and times every launch with CUDA events.  Same kernels, same bits either way. */
 void mpcb_last_solve_profile(MpcHandle* h, double* out6);
 
 /* Bulk phase of the last round-mode solve — the rounds that carried more evaluation requests than the evaluation launch

@@ -42,6 +42,13 @@ struct MpcHandle {
   int spec_live_wide = 4096, spec_live_mid = 12288;    // MPCB_SPEC_LIVE="wide,mid": live-tile thresholds of the policy
   int split_ok = 1;                                    // MPCB_SPLIT env (0: never use the split evaluation)
   int pit_ok = 1;                                      // MPCB_PIT env (0: never use the parallel-in-time evaluation)
+  // Round mode's loop: driven on the device by a CUDA graph (WHILE node; the default: mpcb_solve returns at once), or by
+  // the host (MPCB_LOOP=host; also taken when a per-round diagnostic is on: MPCB_ROUND_LOG, MPCB_EVAL_TRACE)
+  int loop_graph = 1;
+  struct GraphRun { cudaGraphExec_t exec; cudaGraph_t graph; cudaEvent_t done; };
+  std::vector<GraphRun> graph_runs;                    // kept alive until their completion events have fired
+  bool graph_profile_pending = false; cudaStream_t graph_stream = nullptr; int64_t graph_ens = 0;
+  unsigned long long* rs_stamps = nullptr;             // [kStatRounds][2] %globaltimer stamps of a graph-driven solve
   long long eval_trace_round = -1;                     // MPCB_EVAL_TRACE env
   int last_mode = 0;
   int64_t last_rounds = 0;
@@ -208,6 +215,129 @@ int set_smem(MpcHandle* h, K kernel, size_t bytes) {
   return 0;
 }
 
+// Shared-memory carve-out of a kernel whose residency is bounded by registers, not by shared memory: ask for what
+// `ctas_per_sm` resident CTAs use and leave the rest of the 256 KB to L1.  (Left to the driver, a kernel that requests a
+// few KB of dynamic shared memory can get a carve-out sized for many more CTAs than its registers allow: the evaluation
+// launch of the Bezier-road problems, whose vertex scans live in L1, ran 1.6x slower once it asked for 8 KB.)
+template <class K>
+int set_carveout(MpcHandle* h, K kernel, size_t dyn_bytes, int ctas_per_sm) {
+  cudaFuncAttributes fa;
+  CK(cudaFuncGetAttributes(&fa, kernel));
+  const size_t need = (dyn_bytes + fa.sharedSizeBytes + 1024) * (size_t)ctas_per_sm;  // + 1 KB the system reserves per CTA
+  int pct = (int)((need * 100 + 228 * 1024 - 1) / (228 * 1024));
+  if (pct > 100) pct = 100;
+  CK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+  return 0;
+}
+
+constexpr int64_t kStatRounds = 16384;  // rounds whose request counts / time stamps are kept for the solve profile
+
+// Release graph executables whose solves have completed (all of them when `all`).
+void reap_graph_runs(MpcHandle* h, bool all) {
+  for (size_t i = 0; i < h->graph_runs.size();) {
+    auto& gr = h->graph_runs[i];
+    if (all) cudaEventSynchronize(gr.done);
+    if (all || cudaEventQuery(gr.done) == cudaSuccess) {
+      cudaGraphExecDestroy(gr.exec); cudaGraphDestroy(gr.graph); cudaEventDestroy(gr.done);
+      h->graph_runs.erase(h->graph_runs.begin() + (long)i);
+    } else {
+      ++i;
+    }
+  }
+}
+
+// MPCB_LOOP=graph: one graph launch per solve.  WHILE(more) { IF(small) T<small grid> ELSE T<full grid>; E; advance }.
+int launch_graph_loop(MpcHandle* h, cudaStream_t st, void* t_func, void* e_func, KDesc& k, MpcSolverParams& sp, SolveArgs& a,
+                      EvalArgs& e, int64_t t_blocks_full, int block, size_t box_smem, int64_t eblocks, size_t eval_smem, int G,
+                      unsigned round_cap) {
+  reap_graph_runs(h, false);
+  if (h->graph_runs.size() >= 8) reap_graph_runs(h, true);
+  if (!h->rs_stamps) CK(cudaMalloc((void**)&h->rs_stamps, kStatRounds * 2 * sizeof(unsigned long long)));
+  unsigned* ctl = h->rs_counters + 8;
+  a.round = 0; a.round_ptr = ctl + 1;
+  e.round_ptr = ctl + 1; e.counters_base = h->rs_counters; e.key_cnt_base = a.key_cnt; e.round_stats_base = h->rs_stats;
+  e.stamps = h->rs_stamps; e.stat_rounds = (int)kStatRounds; e.trace = nullptr;
+  cudaGraph_t g = nullptr;
+  CK(cudaGraphCreate(&g, 0));
+  cudaGraphConditionalHandle more_h, small_h;
+  CK(cudaGraphConditionalHandleCreate(&more_h, g, 1, cudaGraphCondAssignDefault));
+  CK(cudaGraphConditionalHandleCreate(&small_h, g, 0, cudaGraphCondAssignDefault));
+  cudaGraphNodeParams wp = {};
+  wp.type = cudaGraphNodeTypeConditional;
+  wp.conditional.handle = more_h; wp.conditional.type = cudaGraphCondTypeWhile; wp.conditional.size = 1;
+  cudaGraphNode_t wnode;
+  CK(cudaGraphAddNode(&wnode, g, nullptr, 0, &wp));
+  cudaGraph_t body = wp.conditional.phGraph_out[0];
+  cudaGraphNodeParams ip = {};
+  ip.type = cudaGraphNodeTypeConditional;
+  ip.conditional.handle = small_h; ip.conditional.type = cudaGraphCondTypeIf; ip.conditional.size = 2;
+  cudaGraphNode_t inode;
+  CK(cudaGraphAddNode(&inode, body, nullptr, 0, &ip));
+  cudaGraph_t g_small = ip.conditional.phGraph_out[0], g_full = ip.conditional.phGraph_out[1];
+  // the transition launch: once at most `small_tiles` tiles are alive a grid for that many (plus bucket padding)
+  const unsigned small_tiles = 1024;
+  int64_t t_blocks_small = (((int64_t)small_tiles + (int64_t)MPCB_NKEY * (32 / G)) * G + block - 1) / block;
+  if (t_blocks_small > t_blocks_full) t_blocks_small = t_blocks_full;
+  void* t_args[] = {&k, &sp, &a};
+  cudaKernelNodeParams kp = {};
+  kp.func = t_func; kp.blockDim = dim3((unsigned)block); kp.sharedMemBytes = (unsigned)box_smem; kp.kernelParams = t_args;
+  cudaGraphNode_t tn;
+  kp.gridDim = dim3((unsigned)t_blocks_small);
+  CK(cudaGraphAddKernelNode(&tn, g_small, nullptr, 0, &kp));
+  kp.gridDim = dim3((unsigned)t_blocks_full);
+  CK(cudaGraphAddKernelNode(&tn, g_full, nullptr, 0, &kp));
+  void* e_args[] = {&k, &e};
+  cudaKernelNodeParams ke = {};
+  ke.func = e_func; ke.gridDim = dim3((unsigned)eblocks); ke.blockDim = dim3(256); ke.sharedMemBytes = (unsigned)eval_smem;
+  ke.kernelParams = e_args;
+  cudaGraphNode_t en;
+  CK(cudaGraphAddKernelNode(&en, body, &inode, 1, &ke));
+  unsigned* counters_base = h->rs_counters;
+  unsigned long long* stamps = h->rs_stamps;
+  int stat_rounds = (int)kStatRounds;
+  unsigned st_small = small_tiles, cap = round_cap;
+  void* a_args[] = {&ctl, &counters_base, &more_h, &small_h, &st_small, &cap, &stamps, &stat_rounds};
+  cudaKernelNodeParams ka = {};
+  ka.func = (void*)k_round_advance; ka.gridDim = dim3(1); ka.blockDim = dim3(32); ka.kernelParams = a_args;
+  cudaGraphNode_t an;
+  CK(cudaGraphAddKernelNode(&an, body, &en, 1, &ka));
+  cudaGraphExec_t exec = nullptr;
+  CK(cudaGraphInstantiate(&exec, g, 0));
+  CK(cudaGraphLaunch(exec, st));
+  cudaEvent_t done;
+  CK(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+  CK(cudaEventRecord(done, st));
+  h->graph_runs.push_back({exec, g, done});
+  h->graph_profile_pending = true; h->graph_stream = st; h->graph_ens = e.ens;
+  return 0;
+}
+
+// The profile of a graph-driven solve is read from the device once somebody asks for it (synchronises the solve's stream).
+void fetch_graph_profile(MpcHandle* h) {
+  if (!h->graph_profile_pending) return;
+  h->graph_profile_pending = false;
+  if (cudaStreamSynchronize(h->graph_stream) != cudaSuccess) return;
+  unsigned ctl[4] = {0, 0, 0, 0};
+  if (cudaMemcpy(ctl, h->rs_counters + 8, sizeof(ctl), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+  const int64_t rounds = ctl[1], nr = std::min<int64_t>(rounds, kStatRounds);
+  std::vector<unsigned long long> stamps((size_t)nr * 2);
+  h->rs_stats_host.resize((size_t)nr * 2);
+  if (nr > 0) {
+    if (cudaMemcpy(stamps.data(), h->rs_stamps, stamps.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    if (cudaMemcpy(h->rs_stats_host.data(), h->rs_stats, (size_t)nr * 2 * sizeof(unsigned), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+  }
+  h->last_rounds = rounds; h->launches += 3 * rounds;
+  h->last_eval_ms = h->last_trans_ms = 0.0;
+  h->bulk_eval_ms = h->bulk_trans_ms = h->bulk_grad = h->bulk_val = 0.0; h->bulk_rounds = 0;
+  for (int64_t r = 0; r < nr; ++r) {
+    const double e_ms = (double)(stamps[2 * r + 1] - stamps[2 * r]) * 1e-6;            // evaluation launch (+ the advance node)
+    const double t_ms = r > 0 ? (double)(stamps[2 * r] - stamps[2 * r - 1]) * 1e-6 : 0.0;  // transition launch (+ node scheduling)
+    h->last_eval_ms += e_ms; h->last_trans_ms += t_ms;
+    const double g = h->rs_stats_host[2 * r], v = h->rs_stats_host[2 * r + 1];
+    if (g + v > (double)h->graph_ens) { h->bulk_eval_ms += e_ms; h->bulk_trans_ms += t_ms; h->bulk_grad += g; h->bulk_val += v; h->bulk_rounds++; }
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -282,6 +412,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
   }
   if (const char* e = std::getenv("MPCB_SPLIT")) h->split_ok = std::atoi(e) != 0;
   if (const char* e = std::getenv("MPCB_PIT")) h->pit_ok = std::atoi(e) != 0;
+  if (const char* e = std::getenv("MPCB_LOOP")) h->loop_graph = std::strcmp(e, "host") != 0;
   if (const char* e = std::getenv("MPCB_EVAL_TRACE")) h->eval_trace_round = std::atoll(e);
   *out = h;
   return MPCB_OK;
@@ -293,7 +424,8 @@ void mpcb_destroy(MpcHandle* h) {
                   (void*)h->ifail, (void*)h->trace, (void*)h->dev, (void*)h->rs_d, (void*)h->rs_i, (void*)h->rs_req,
                   (void*)h->rs_escr, (void*)h->rs_keys})
     free_scratch(h, q);
-  cudaFree(h->queue); cudaFree(h->rs_stats); cudaFree(h->rs_counters);
+  cudaFree(h->queue); cudaFree(h->rs_stats); cudaFree(h->rs_counters); cudaFree(h->rs_stamps);
+  for (auto& gr : h->graph_runs) { cudaEventSynchronize(gr.done); cudaGraphExecDestroy(gr.exec); cudaGraphDestroy(gr.graph); cudaEventDestroy(gr.done); }
   if (h->rs_counters_host) cudaFreeHost(h->rs_counters_host);
   for (cudaEvent_t ev : h->rs_ev) if (ev) cudaEventDestroy(ev);
   if (h->pin) cudaFreeHost(h->pin);
@@ -303,14 +435,16 @@ void mpcb_destroy(MpcHandle* h) {
 }
 
 const char* mpcb_last_error(MpcHandle* h) { return h ? h->err.c_str() : "null handle"; }
-int64_t mpcb_launch_count(MpcHandle* h) { return h ? h->launches : 0; }
+int64_t mpcb_launch_count(MpcHandle* h) { if (h) fetch_graph_profile(h); return h ? h->launches : 0; }
 void mpcb_last_solve_profile(MpcHandle* h, double* out) {
   if (!h || !out) return;
+  fetch_graph_profile(h);
   out[0] = h->last_mode; out[1] = h->last_tile; out[2] = (double)h->last_rounds;
   out[3] = h->last_eval_ms; out[4] = h->last_trans_ms; out[5] = h->last_mode ? (double)h->last_rounds : 1.0;
 }
 void mpcb_last_solve_bulk_profile(MpcHandle* h, double* out) {
   if (!h || !out) return;
+  fetch_graph_profile(h);
   out[0] = (double)h->bulk_rounds; out[1] = h->bulk_eval_ms; out[2] = h->bulk_trans_ms; out[3] = h->bulk_grad; out[4] = h->bulk_val;
 }
 
@@ -520,9 +654,8 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     const int64_t ens = wblocks * 256;
     // the grid always covers every SM: CTAs beyond `wblocks` only take parallel-in-time requests (shared memory only)
     const int64_t eblocks = h->num_sms;
-    const size_t pit_smem = sizeof(double) * (size_t)(k.model_id == MPCB_MODEL_PACEJKA6 ? fm_pit_doubles<MPCB_MODEL_PACEJKA6>(k.N)
-                                                                                         : fm_pit_doubles<MPCB_MODEL_KINEMATIC4>(k.N));
-    const size_t eval_smem = road_smem + pit_smem;
+    const size_t pit_smem = sizeof(double) * (size_t)fm_pit_doubles<MPCB_MODEL_PACEJKA6>(k.N);  // (Fm<KINEMATIC4>::PIT is false)
+    const size_t eval_smem = road_smem + (h->pit_ok && k.model_id == MPCB_MODEL_PACEJKA6 ? pit_smem : 0);
     if (eval_smem > 200 * 1024) return fail(h, MPCB_E_UNSUPPORTED, "mpcb_solve: road table + evaluation buffers exceed shared memory");
     if ((rc = grow(h, &h->rs_d, &h->rs_d_cap, (size_t)MPCB_SD_ROWS * ns * sizeof(double), st))) return rc;
     if ((rc = grow(h, &h->rs_i, &h->rs_i_cap, (size_t)MPCB_SI_ROWS * ns * sizeof(int32_t), st))) return rc;
@@ -558,19 +691,47 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
 #define MPCB_LAUNCH_T(MODEL, GG)                                                               \
   do {                                                                                         \
     if (round == 0 && (rc = set_smem(h, k_solve<MODEL, GG, true>, box_smem))) return rc;       \
-    k_solve<MODEL, GG, true><<<(unsigned)blocks, block, box_smem, st>>>(k, *sp, a);            \
+    k_solve<MODEL, GG, true><<<(unsigned)t_blocks, block, box_smem, st>>>(k, *sp, a);          \
   } while (0)
 #define MPCB_LAUNCH_T_G(MODEL)                                                                 \
   switch (G) {                                                                                 \
     case 8: MPCB_LAUNCH_T(MODEL, 8); break;                                                    \
     default: MPCB_LAUNCH_T(MODEL, 1); break;                                                   \
   }
-    if (k.model_id == MPCB_MODEL_PACEJKA6) { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_PACEJKA6>, eval_smem))) return rc; }
-    else { if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_KINEMATIC4>, eval_smem))) return rc; }
+    if (k.model_id == MPCB_MODEL_PACEJKA6) {
+      if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_PACEJKA6>, eval_smem))) return rc;
+      if ((rc = set_carveout(h, k_eval_requests<MPCB_MODEL_PACEJKA6>, eval_smem, 1))) return rc;
+    } else {
+      if ((rc = set_smem(h, k_eval_requests<MPCB_MODEL_KINEMATIC4>, eval_smem))) return rc;
+      if ((rc = set_carveout(h, k_eval_requests<MPCB_MODEL_KINEMATIC4>, eval_smem, 1))) return rc;
+    }
     int64_t round = 0;
+    // transition grid: every tile at first; after each chunk of rounds the live-tile count the host has just read bounds
+    // it from above (tiles only finish), so the last rounds of a batch launch a few CTAs instead of thousands that exit
+    int64_t t_blocks = blocks;
     // no instance can need more: <= ~40 rounds per PANOC iteration (9 trials x descent-lemma steps) over at most
     // max_iter iterations per PANOC run and ~8 runs of the tolerance continuation; a guard against a hang, not a limit
     const int64_t round_cap = std::min<int64_t>(4000000, 64 + (int64_t)40 * (sp->max_iter + 8) * 10);
+    if (h->loop_graph && !h->round_log && h->eval_trace_round < 0) {
+      // device-driven rounds: ONE graph launch, asynchronous on the caller's stream (include/mpcb200.h)
+      if (!h->rs_stats) CK(cudaMalloc((void**)&h->rs_stats, kStatRounds * 2 * sizeof(unsigned)));
+      void *t_func = nullptr, *e_func = nullptr;
+      if (k.model_id == MPCB_MODEL_PACEJKA6) {
+        e_func = (void*)k_eval_requests<MPCB_MODEL_PACEJKA6>;
+        t_func = G == 8 ? (void*)k_solve<MPCB_MODEL_PACEJKA6, 8, true> : (void*)k_solve<MPCB_MODEL_PACEJKA6, 1, true>;
+        if ((rc = G == 8 ? set_smem(h, k_solve<MPCB_MODEL_PACEJKA6, 8, true>, box_smem) : set_smem(h, k_solve<MPCB_MODEL_PACEJKA6, 1, true>, box_smem))) return rc;
+      } else {
+        e_func = (void*)k_eval_requests<MPCB_MODEL_KINEMATIC4>;
+        t_func = G == 8 ? (void*)k_solve<MPCB_MODEL_KINEMATIC4, 8, true> : (void*)k_solve<MPCB_MODEL_KINEMATIC4, 1, true>;
+        if ((rc = G == 8 ? set_smem(h, k_solve<MPCB_MODEL_KINEMATIC4, 8, true>, box_smem) : set_smem(h, k_solve<MPCB_MODEL_KINEMATIC4, 1, true>, box_smem))) return rc;
+      }
+      KDesc kk = k;
+      MpcSolverParams spp = *sp;
+      if ((rc = launch_graph_loop(h, st, t_func, e_func, kk, spp, a, e, blocks, block, box_smem, eblocks, eval_smem, G,
+                                  (unsigned)std::min<int64_t>(round_cap, 0x7fffffff))))
+        return rc;
+      return leave(h, st);
+    }
     int chunk = 48;
     for (cudaEvent_t& ev : h->rs_ev) if (!ev) CK(cudaEventCreate(&ev));
     if (h->debug_timers >= 2) {
@@ -589,7 +750,6 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
       CK(cudaMemsetAsync(h->dbg, 0, (size_t)(ns / 32 + 2) * 2 * sizeof(long long), st));
     }
     h->last_eval_ms = 0.0; h->last_trans_ms = 0.0;
-    constexpr int64_t kStatRounds = 16384;  // request counts of the first rounds (later ones are the tail anyway)
     if (!h->rs_stats) CK(cudaMalloc((void**)&h->rs_stats, kStatRounds * 2 * sizeof(unsigned)));
     h->rs_t_ms.clear(); h->rs_e_ms.clear();
     for (;;) {
@@ -650,6 +810,11 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
       }
       const unsigned* last = h->rs_counters_host + 4 * (chunk - 1);
       if (last[0] == 0 && last[1] == 0) break;
+      {
+        const int64_t live = last[3];
+        const int64_t need = ((live + (int64_t)MPCB_NKEY * (32 / G)) * G + block - 1) / block;
+        t_blocks = need < blocks ? (need > 0 ? need : 1) : blocks;
+      }
       if (round > round_cap) return fail(h, MPCB_E_CUDA, "mpcb_solve: round cap exceeded");
       chunk = 24;
     }

@@ -27,6 +27,7 @@ template <int MODEL> struct Fm;
 // ---- Pacejka-6 (car_dynamics.py:93-129): q = (phi, vx, vy, omega) ------------------------------
 template <> struct Fm<MPCB_MODEL_PACEJKA6> {
   static constexpr int NX = 6, NQ = 4, ND = 5;  // directions: vx, vy, omega, d, delta
+  static constexpr bool PIT = true;             // thin rounds use the parallel-in-time evaluation (eval_fm_pit)
   struct Lin {
     double s, c, f0, f1;
     double a11, a12, a13, a21, a22, a23, a31, a32, a33;
@@ -242,6 +243,12 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
 // ---- Kinematic-4 (dynamics.py:144-173): q = (phi, v), directions v, d, delta ---------------------
 template <> struct Fm<MPCB_MODEL_KINEMATIC4> {
   static constexpr int NX = 4, NQ = 2, ND = 3;
+  // No parallel-in-time evaluation for this model.  Measured (B200, config 3: 8192 instances, N = 40, obstacles, Bezier
+  // roads): merely instantiating eval_fm_pit<KINEMATIC4> inside k_eval_requests slowed the kernel's OTHER paths by 58 %
+  // (evaluation launches 1.18 -> 1.86 s per batch, the psi-only bulk rounds included; same registers, same stack) — a
+  // code-generation interaction, not the algorithm — while the thin rounds gained 6 %.  The model call is cheap here
+  // (one sincos): the latency of a request is in the stage costs, not in a dependent chain of model calls.
+  static constexpr bool PIT = false;
   struct Lin { double s, c, v, sb_lr, cb_lr_db, db, acc, mu; };
   template <bool GRAD>
   static MPCB_DEV void call(const double* q, const StageU& su, const VehP& v, double* kp, double* kq, Lin& L) {

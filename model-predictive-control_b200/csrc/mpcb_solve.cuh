@@ -55,7 +55,8 @@ struct SolveArgs {
   unsigned long long* queue;
   long long* dbg;  // optional [warps, 4]: cycles in evaluation / transition phases, rounds, gradient rounds
   // ---- round mode (k_solve<.., ROUND = true> + k_eval_requests, see below) ----
-  int round;                 // index of this transition launch
+  int round;                 // index of this transition launch (host-driven loop)
+  const unsigned* round_ptr; // graph-driven loop: the round index lives in device memory (ctl[1]); null otherwise
   double* sd;                // saved lane state, doubles  [MPCB_SD_ROWS, ns]
   int32_t* si;               // saved lane state, ints     [MPCB_SI_ROWS, ns]
   int32_t* req_want;         // [ns] evaluation request of every lane: 0 none, 1 psi, 2 psi + grad psi, 3 psi + states
@@ -121,7 +122,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   const int n = d.n, m = d.m, mem = sp.lbfgs_mem;
   double* sroad = smem;
   double* sbox = smem + (!ROUND && a.ra.in_smem ? a.ra.R * road_smem_doubles(d.S) : 0);  // lb[n], ub[n]
-  if (a.fin_ns && threadIdx.x == 0 && (!ROUND || a.round == 0)) {  // start of the solve: earliest CTA of the first launch
+  const int rnd = (ROUND && a.round_ptr) ? (int)*a.round_ptr : a.round;  // this launch's round
+  if (a.fin_ns && threadIdx.x == 0 && (!ROUND || rnd == 0)) {  // start of the solve: earliest CTA of the first launch
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     atomicMin(&a.fin_ns[a.B], t);
@@ -136,8 +138,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     if (a.ra.in_smem) stage_roads(sroad, a.ra.road, a.ra.R, d.S);
   } else {
     constexpr int TPW = 32 / G;  // tiles per warp
-    if (a.round > 0) {
-      const int32_t* kc = a.key_cnt + MPCB_NKEY * (a.round & 1);
+    if (rnd > 0) {
+      const int32_t* kc = a.key_cnt + MPCB_NKEY * (rnd & 1);
       int64_t g = tile_sel, start = 0;
       int key = -1;
       int64_t off = 0;
@@ -154,13 +156,13 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       // `start` = padded number of groups: a CTA past it has nothing to do (late in a batch: most of the grid)
       if ((int64_t)blockIdx.x * (blockDim.x / G) >= start) {
         if (blockIdx.x == 0 && threadIdx.x == 0) {  // (no live tile at all: the batch is done)
-          unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
+          unsigned* nx = a.counters + 4 * ((rnd + 1) & 1);
           nx[0] = 0u; nx[1] = 0u; nx[2] = 0u; nx[3] = 0u;
         }
         return;
       }
       if (key < 0 || key >= MPCB_NKEY) notile = true;
-      else tile_sel = a.key_list[((int64_t)(a.round & 1) * MPCB_NKEY + key) * a.nt + off];
+      else tile_sel = a.key_list[((int64_t)(rnd & 1) * MPCB_NKEY + key) * a.nt + off];
     } else if (tile_sel >= a.nt) {
       notile = true;
     }
@@ -249,7 +251,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   X(alm_i) X(inner_total) X(pstatus) X(n_val) X(n_grad) X(t_rounds) X(dbg_fd) X(dbg_lemma) X(dbg_slide) X(c_idx) X(spec_for) X(lsW) X(n_ifail) X(last_c)
   bool dead = notile;  // round mode: this group has no tile / its tile has no instance left
   if constexpr (ROUND) {
-    if (a.round > 0 && !notile) {
+    if (rnd > 0 && !notile) {
       const int fl = a.si[slot];
       exhausted = fl & 1; fd_ready = fl & 2; c_valid = fl & 4; c_pend = fl & 8; c_rq = fl & 16; c_fb = fl & 32;
       c_acc = fl & 64; c_started = fl & 128; fd_done = fl & 256; c_needg = fl & 512;
@@ -1020,9 +1022,9 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     if constexpr (ROUND) {
       // ================= round mode: publish the request, save the registers, leave ===============
       // (the evaluation runs in k_eval_requests over the compacted request lists)
-      unsigned* cnt = a.counters + 4 * (a.round & 1);
+      unsigned* cnt = a.counters + 4 * (rnd & 1);
       if (blockIdx.x == 0 && threadIdx.x == 0) {  // the other parity's counters: last read by the previous evaluation launch
-        unsigned* nx = a.counters + 4 * ((a.round + 1) & 1);
+        unsigned* nx = a.counters + 4 * ((rnd + 1) & 1);
         nx[0] = 0u; nx[1] = 0u; nx[2] = 0u; nx[3] = 0u;
       }
       if (!dead) {
@@ -1059,12 +1061,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         int rank = -1;
         if (l == 0 && !dead) rank = atomicAdd(&s_kcnt[key], 1);
         __syncthreads();
-        int32_t* kc_out = a.key_cnt + MPCB_NKEY * ((a.round + 1) & 1);
+        int32_t* kc_out = a.key_cnt + MPCB_NKEY * ((rnd + 1) & 1);
         if (threadIdx.x < MPCB_NKEY && s_kcnt[threadIdx.x] > 0)
           s_kbase[threadIdx.x] = atomicAdd(&kc_out[threadIdx.x], s_kcnt[threadIdx.x]);
         __syncthreads();
         if (rank >= 0)
-          a.key_list[((int64_t)((a.round + 1) & 1) * MPCB_NKEY + key) * nt + s_kbase[key] + rank] = (int32_t)tile;
+          a.key_list[((int64_t)((rnd + 1) & 1) * MPCB_NKEY + key) * nt + s_kbase[key] + rank] = (int32_t)tile;
       }
       if (!was_dead) {  // tiles that were already dead keep their saved flags
         a.si[slot] = (int)exhausted | (int)fd_ready << 1 | (int)c_valid << 2 | (int)c_pend << 3 | (int)c_rq << 4 | (int)c_fb << 5 |
@@ -1140,6 +1142,13 @@ struct EvalArgs {
   unsigned* ctl;            // [4] control words read by the next transition launch: [0] live tiles
   int32_t* key_cnt_zero;    // [MPCB_NKEY] bucket counts the next transition launch appends to (zeroed here)
   unsigned* round_stats;    // [2] this round's (gradient, psi-only) request counts, kept for the solve profile; or null
+  // graph-driven loop (round_ptr != null): the per-round pointers above are derived in the kernel from the round index
+  const unsigned* round_ptr;
+  unsigned* counters_base;        // [2][4]
+  int32_t* key_cnt_base;          // [2][MPCB_NKEY]
+  unsigned* round_stats_base;     // [stat_rounds][2]
+  unsigned long long* stamps;     // [stat_rounds][2] %globaltimer at the start of the evaluation launch / end of the round
+  int stat_rounds;
   double* escr;             // stage-Jacobian scratch of the evaluating lanes [N * K, ens]
   long long* trace;         // diagnostic (MPCB_EVAL_TRACE=round): per chunk [cycles, first slot] or null
   int split_ok;             // 0: never use the split evaluation (MPCB_SPLIT=0)
@@ -1166,6 +1175,17 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const int lane = threadIdx.x & 31;
   const int64_t eslot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const Vec scr{e.escr + eslot, e.ens};
+  if (e.round_ptr) {  // graph-driven loop: this round's buffers
+    const unsigned r = *e.round_ptr;
+    e.counters = e.counters_base + 4 * (r & 1u);
+    e.key_cnt_zero = e.key_cnt_base + MPCB_NKEY * (r & 1u);
+    e.round_stats = r < (unsigned)e.stat_rounds ? e.round_stats_base + 2 * r : nullptr;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && r < (unsigned)e.stat_rounds) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      e.stamps[2 * r] = t;
+    }
+  }
   const unsigned ng = e.counters[0], nv = e.counters[1];
   if (blockIdx.x == 0 && threadIdx.x == 0 && e.ctl) e.ctl[0] = e.counters[3];
   if (blockIdx.x == 0 && threadIdx.x == 0 && e.round_stats) { e.round_stats[0] = ng; e.round_stats[1] = nv; }
@@ -1173,7 +1193,7 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const unsigned cv = (nv + 31u) >> 5;
   // Few gradient requests (each can have a CTA of its own next to the psi-only chunks): parallel-in-time evaluation,
   // one request per CTA from the END of the grid (the psi-only chunks are handed out from its start).
-  const bool pit = e.pit_ok && ng > 0 && ng + (cv < 8u ? cv : 8u) <= gridDim.x;
+  const bool pit = Fm<MODEL>::PIT && e.pit_ok && ng > 0 && ng + (cv < 8u ? cv : 8u) <= gridDim.x;
   if (pit) {
     double* pit_sm = smem + (e.ra.in_smem ? e.ra.R * road_smem_doubles(d.S) : 0);
     const unsigned ridx = gridDim.x - 1u - blockIdx.x;
@@ -1184,7 +1204,8 @@ k_eval_requests(KDesc d, EvalArgs e) {
       RoadView r = road_view(e.ra, sroad, d.S, b);
       Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
                 d.bounded ? e.sig_base + tile : nullptr, 1, e.nt};
-      const double v = eval_fm_pit<MODEL>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], e.ns}, Vec{e.req_g[slot], e.ns}, pit_sm, !d.exact);
+      double v = 0.0;
+      if constexpr (Fm<MODEL>::PIT) v = eval_fm_pit<MODEL>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], e.ns}, Vec{e.req_g[slot], e.ns}, pit_sm, !d.exact);
       if (threadIdx.x == 0) e.req_val[slot] = v;
       return;  // (a CTA with a parallel-in-time request takes no chunks: nb below keeps them apart)
     }
@@ -1262,6 +1283,28 @@ k_eval_requests(KDesc d, EvalArgs e) {
       }
     }
   }
+}
+
+// ---- graph-driven loop: the node that closes a round ----------------------------------------------------
+// Runs after the evaluation launch of round r inside the WHILE body of the solve's CUDA graph: decides whether another
+// round is needed (any request published), advances the round index the kernels read, picks the transition launch's
+// grid for the next round (the IF node: a small grid once few tiles are alive) and stamps the time.
+__global__ void k_round_advance(unsigned* ctl, const unsigned* counters_base, cudaGraphConditionalHandle more_h,
+                                cudaGraphConditionalHandle small_h, unsigned small_tiles, unsigned round_cap,
+                                unsigned long long* stamps, int stat_rounds) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const unsigned r = ctl[1];
+  const unsigned* c = counters_base + 4 * (r & 1u);
+  const bool more = (c[0] + c[1]) > 0u && r + 1u < round_cap;
+  if (r < (unsigned)stat_rounds) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    stamps[2 * r + 1] = t;
+  }
+  ctl[1] = r + 1u;
+  if (!more && (c[0] + c[1]) > 0u) ctl[2] = 1u;  // stopped by the round cap
+  cudaGraphSetConditional(more_h, more ? 1u : 0u);
+  cudaGraphSetConditional(small_h, c[3] <= small_tiles ? 1u : 0u);  // c[3]: tiles still solving after this round
 }
 
 }  // namespace mpcb

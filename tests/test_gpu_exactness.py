@@ -290,3 +290,48 @@ def test_parallel_in_time_evaluation_changes_nothing(mp, problem, monkeypatch):
             _, _, U, _, st = _solve_lane_change(mp, 40, 8, seed=78)
         out.append((U, st))
     _assert_same_solution(out[0], out[1], f"{problem}: chunked evaluations vs parallel-in-time")
+
+
+# ------------------------------------------------------------------ 6. the device-driven round loop (CUDA graph WHILE node)
+@pytest.mark.parametrize("problem", ["pacejka_B1_N12", "pacejka_B3000_N20", "pacejka_bounded_B200_N12", "kinematic_obstacles_B300_N20"])
+def test_graph_driven_loop_equals_host_loop(mp, problem, monkeypatch):
+    """MPCB_LOOP=graph: one graph launch per solve — WHILE(any request) { transition; evaluation; advance } with the round
+    index, the stop test and the choice of the transition grid on the device.  Same kernels on the same data: the same bits
+    as the host-driven loop; and the call is asynchronous (it returns while the GPU is still solving)."""
+    import time
+    import torch
+    monkeypatch.setenv("MPCB_MODE", "rounds")
+    out, t_call, t_total = [], {}, {}
+    for loop in ("host", "graph"):
+        monkeypatch.setenv("MPCB_LOOP", loop)
+        if problem == "pacejka_B1_N12":
+            args = (12, 1, 8)
+        elif problem == "pacejka_B3000_N20":
+            args = (20, 3000, 9)
+        if problem.startswith("pacejka_B"):
+            prob, w = _tracking(mp, args[0], args[1], seed=args[2])
+            dev = prob.device
+            x0, road = torch.tensor(w["x0"], device=dev), torch.tensor(w["road"], device=dev)
+            ridx = torch.tensor(w["road_idx"], device=dev)
+            prob.solve(x0, road, torch.tensor(w["U0"], device=dev), road_idx=ridx)   # warm: allocations, graph build paths
+            U = torch.tensor(w["U0"], device=dev)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            U, _, st = prob.solve(x0, road, U, road_idx=ridx)
+            t_call[loop] = time.perf_counter() - t0
+            torch.cuda.synchronize()
+            t_total[loop] = time.perf_counter() - t0
+            prof = prob.last_solve_profile()
+            assert prof["mode"] == "rounds" and prof["rounds"] > 0 and prof["eval_ms"] > 0
+        elif problem.startswith("pacejka_bounded"):
+            _, _, U, _, st = _solve_tracking(mp, 12, 200, seed=31, flags=mp.FLAG_BOUNDED_D, lam=True, D_lower=[-np.inf] * 6,
+                                             D_upper=[np.inf, np.inf, np.inf, -1.0, np.inf, np.inf])
+        else:
+            _, _, U, _, st = _solve_lane_change(mp, 20, 300, seed=78)
+        out.append((U, st))
+    _assert_same_solution(out[0], out[1], f"{problem}: host-driven vs graph-driven rounds")
+    if problem == "pacejka_B3000_N20":
+        print(f"call returned after {t_call['graph'] * 1e3:.1f} ms of a {t_total['graph'] * 1e3:.1f} ms solve (host loop: "
+              f"{t_call['host'] * 1e3:.1f} of {t_total['host'] * 1e3:.1f} ms)")
+        assert t_call["graph"] < 0.25 * t_total["graph"]       # asynchronous on the caller's stream
+        assert t_call["host"] > 0.9 * t_total["host"]          # the host loop blocks

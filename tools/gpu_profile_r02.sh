@@ -4,6 +4,7 @@
 # Usage (GPU box, repo root): bash tools/gpu_profile_r02.sh
 out=gpurun_out
 tag=r02
+export MPCB_LOOP=host   # ncu profiles the launches of the host-driven loop (same kernels as the graph-driven default)
 mkdir -p $out
 BENCH="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-api-leg"
 $BENCH > $out/${tag}_bench_plain.json 2> $out/${tag}_bench_plain.err && \
