@@ -44,6 +44,9 @@ extern "C" {
 #define MPCB_FLAG_LANE 1      /* add u_trgl + u_rbd (dpf_test.py:45-54) to every stage */
 #define MPCB_FLAG_OBST 2      /* add dnf (dpf_test.py:81-102) for n_obs obstacles to every stage */
 #define MPCB_FLAG_BOUNDED_D 4 /* state constraints g (main.py:43-52) are bounded by D_lower/D_upper */
+#define MPCB_FLAG_SAFE_DIST 16 /* n_obs more rows of g per stage: the safe-distance ellipse around every obstacle,
+                                 g = 1 - (dx / x_s)^2 - (dy / y_s)^2 <= 0 with (x_s, y_s) = get_safe_distances
+                                 (dpf_test.py:57-64), D = (-inf, 0]; handled by the ALM like the state rows */
 #define MPCB_FLAG_EXACT 8     /* diagnostic: solver shortcuts off (early line-search rejection, descent-lemma steps
                                  decided without psi(x̂+), evaluations cut at a blown-up state); same iterates, slower;
                                  MPCB_EXACT=1 in the environment sets it for every handle */
@@ -93,6 +96,8 @@ typedef struct MpcProblemDesc {
   /* state constraints g_i = y_i^2 - g_offset[i] (main.py:46-51) and their box D */
   double g_offset[6];
   double D_lower[6], D_upper[6]; /* +-inf = unbounded (the reference leaves D at +-inf, main.py:57) */
+  /* safe distances, dpf_test.py:6,57-64: x_s = x_0/2 + (v_x - v_x,obs)^2 / (2 a_x_max), same in y */
+  double safe_x0, safe_y0, safe_ax_max, safe_ay_max; /* 5, 3, 3, 1 */
 } MpcProblemDesc;
 
 /* Solver parameters: alpaqa 0.0.1 defaults with the overrides of reference controller.py:27-48.

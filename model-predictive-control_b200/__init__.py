@@ -10,7 +10,7 @@ compute entry point raises if it is missing or no GPU is present (no CPU fallbac
 __version__ = "0.1.0"
 
 from . import _ffi  # noqa: F401
-from ._ffi import (FLAG_BOUNDED_D, FLAG_EXACT, FLAG_LANE, FLAG_OBST, MODEL_KINEMATIC4, MODEL_PACEJKA6, ROAD_BEZIER,  # noqa: F401
+from ._ffi import (FLAG_BOUNDED_D, FLAG_EXACT, FLAG_LANE, FLAG_OBST, FLAG_SAFE_DIST, MODEL_KINEMATIC4, MODEL_PACEJKA6, ROAD_BEZIER,  # noqa: F401
                    ROAD_PER_INSTANCE, ROAD_SHARED, ROAD_TABLE, MpcbError)
 
 

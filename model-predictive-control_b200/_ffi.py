@@ -13,7 +13,7 @@ LIB_PATH = os.environ.get("MPCB_LIB") or os.path.join(_HERE, "libmpcb200.so")
 # model / road / flag constants (include/mpcb200.h)
 MODEL_PACEJKA6, MODEL_KINEMATIC4 = 0, 1
 ROAD_SHARED, ROAD_TABLE, ROAD_PER_INSTANCE, ROAD_BEZIER = 0, 1, 2, 3
-FLAG_LANE, FLAG_OBST, FLAG_BOUNDED_D, FLAG_EXACT = 1, 2, 4, 8
+FLAG_LANE, FLAG_OBST, FLAG_BOUNDED_D, FLAG_EXACT, FLAG_SAFE_DIST = 1, 2, 4, 8, 16
 STATUS_UNKNOWN, STATUS_CONVERGED, STATUS_MAX_TIME, STATUS_MAX_ITER = 0, 1, 2, 3
 STATUS_NOT_FINITE, STATUS_NO_PROGRESS, STATUS_INTERRUPTED = 4, 5, 6
 E_ARG, E_CUDA, E_UNSUPPORTED, E_NODEVICE = -1, -2, -3, -4
@@ -32,6 +32,7 @@ class MpcProblemDesc(C.Structure):
         ("obs_Af", C.c_double), ("obs_b", C.c_double), ("obs_sigma_x", C.c_double),
         ("obs_sigma_y", C.c_double), ("obs_alpha_div", C.c_double),
         ("g_offset", C.c_double * 6), ("D_lower", C.c_double * 6), ("D_upper", C.c_double * 6),
+        ("safe_x0", C.c_double), ("safe_y0", C.c_double), ("safe_ax_max", C.c_double), ("safe_ay_max", C.c_double),
     ]
 
 

@@ -135,7 +135,8 @@ KDesc make_kdesc(const MpcProblemDesc& d) {
   std::memset(&k, 0, sizeof(k));
   k.model_id = d.model_id; k.N = d.N; k.S = d.S; k.n_sub = d.n_sub;
   k.nx = d.model_id == MPCB_MODEL_KINEMATIC4 ? 4 : 6;
-  k.n = 2 * d.N; k.m = k.nx * d.N; k.n_obs = d.n_obs; k.flags = d.flags; k.road_mode = d.road_mode;
+  k.rows = k.nx + ((d.flags & MPCB_FLAG_SAFE_DIST) ? d.n_obs : 0);
+  k.n = 2 * d.N; k.m = k.rows * d.N; k.n_obs = d.n_obs; k.flags = d.flags; k.road_mode = d.road_mode;
   k.n_roads = d.road_mode == MPCB_ROAD_TABLE ? d.n_roads : 1;
   k.h = d.Ts / d.n_sub; k.Ts = d.Ts; k.v_ref = d.v_ref;
   for (int i = 0; i < 6; ++i) { k.c[i] = d.c[i]; k.g_off[i] = d.g_offset[i]; k.D_lo[i] = d.D_lower[i]; k.D_hi[i] = d.D_upper[i]; }
@@ -150,9 +151,15 @@ KDesc make_kdesc(const MpcProblemDesc& d) {
   for (int i = 0; i < 6; ++i) if (!(d.c[i] >= 0.0)) k.psi_nonneg = 0;
   if ((d.flags & MPCB_FLAG_LANE) && !(d.lane_a >= 0.0 && d.lane_b >= 0.0)) k.psi_nonneg = 0;
   if ((d.flags & MPCB_FLAG_OBST) && !(d.obs_Af >= 0.0)) k.psi_nonneg = 0;
-  if (d.flags & MPCB_FLAG_BOUNDED_D)
+  k.safe_x0 = d.safe_x0; k.safe_y0 = d.safe_y0; k.safe_ax = d.safe_ax_max; k.safe_ay = d.safe_ay_max;
+  if (d.flags & MPCB_FLAG_BOUNDED_D) {
     for (int i = 0; i < k.nx; ++i)
       if (!std::isinf(d.D_lower[i]) || !std::isinf(d.D_upper[i])) k.bounded = 1;
+  } else {  // the state rows are live only with MPCB_FLAG_BOUNDED_D: an infinite box makes them vacuous
+    const double inf = std::numeric_limits<double>::infinity();
+    for (int i = 0; i < 6; ++i) { k.D_lo[i] = -inf; k.D_hi[i] = inf; }
+  }
+  if ((d.flags & MPCB_FLAG_SAFE_DIST) && d.n_obs > 0) k.bounded = 1;
   return k;
 }
 
@@ -358,6 +365,7 @@ void mpcb_default_desc(MpcProblemDesc* d, int32_t model_id, int32_t N, int32_t S
   const double off[6] = {20, 1, 1, 2, 1, 0.1};                 // main.py:46-51
   const double inf = std::numeric_limits<double>::infinity();
   for (int i = 0; i < 6; ++i) { d->g_offset[i] = off[i]; d->D_lower[i] = -inf; d->D_upper[i] = inf; }  // main.py:57
+  d->safe_x0 = 5.0; d->safe_y0 = 3.0; d->safe_ax_max = 3.0; d->safe_ay_max = 1.0;                      // dpf_test.py:6
 }
 
 void mpcb_default_solver_params(MpcSolverParams* sp, int32_t N) {
@@ -504,7 +512,7 @@ int mpcb_rollout(MpcHandle* h, int64_t B, const double* x0, const double* U, con
   if (!h || B < 0) return fail(h, MPCB_E_ARG, "mpcb_rollout: bad argument");
   if (B == 0) return MPCB_OK;
   if (!x0 || !U || !p || !road) return fail(h, MPCB_E_ARG, "mpcb_rollout: null argument");
-  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if ((h->kd.flags & (MPCB_FLAG_OBST | MPCB_FLAG_SAFE_DIST)) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST / MPCB_FLAG_SAFE_DIST");
   cudaStream_t st = (cudaStream_t)stream;
   RoadArg ra; size_t smem;
   int rc;
@@ -528,7 +536,7 @@ int mpcb_value_grad(MpcHandle* h, int64_t B, const double* x0, const double* U, 
   if (!h || B < 0) return fail(h, MPCB_E_ARG, "mpcb_value_grad: bad argument");
   if (B == 0) return MPCB_OK;
   if (!x0 || !U || !p || !road || !cost_out || !grad_out) return fail(h, MPCB_E_ARG, "mpcb_value_grad: null argument");
-  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if ((h->kd.flags & (MPCB_FLAG_OBST | MPCB_FLAG_SAFE_DIST)) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST / MPCB_FLAG_SAFE_DIST");
   cudaStream_t st = (cudaStream_t)stream;
   RoadArg ra; size_t smem;
   int rc;
@@ -565,7 +573,7 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     return fail(h, MPCB_E_ARG, "mpcb_solve: null argument");
   if (sp->lbfgs_mem < 1 || sp->lbfgs_mem > 2 * MPCB_MAX_N || sp->max_iter < 0 || sp->max_no_progress < 1 || sp->alm_max_iter < 1)
     return fail(h, MPCB_E_ARG, "mpcb_solve: bad solver params (lbfgs_mem in [1, 2 MPCB_MAX_N], max_iter >= 0, max_no_progress >= 1, alm_max_iter >= 1)");
-  if ((h->kd.flags & MPCB_FLAG_OBST) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST");
+  if ((h->kd.flags & (MPCB_FLAG_OBST | MPCB_FLAG_SAFE_DIST)) && h->kd.n_obs > 0 && !obs) return fail(h, MPCB_E_ARG, "obs required with MPCB_FLAG_OBST / MPCB_FLAG_SAFE_DIST");
   cudaStream_t st = (cudaStream_t)stream;
   const KDesc& k = h->kd;
   int rc;

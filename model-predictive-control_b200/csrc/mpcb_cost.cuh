@@ -280,6 +280,35 @@ MPCB_DEV double alm_row(double g, double lam, double Sig, double lo, double hi, 
   return 0.5 * Sig * dz * dz;
 }
 
+// dpf_test.py:57-64 get_safe_distances + the ellipse of those semi-axes around an obstacle as a constraint row:
+// g = 1 - (dx / x_s)^2 - (dy / y_s)^2 <= 0, x_s = x_0/2 + (v_x - v_x,obs)^2 / (2 a_x_max) (same in y), velocities in
+// the world frame: (v cos phi, v sin phi) for Kinematic-4, R(phi) (vx, vy) for Pacejka-6.  gy (nullable) is
+// ACCUMULATED with weight w: gy += w dg/dy.
+template <int MODEL>
+MPCB_DEV double safe_dist_row(const KDesc& d, const double* y, double xo, double yo, double po, double vo, double w, double* gy) {
+  double s, c, so, co;
+  sincos(y[2], &s, &c);
+  sincos(po, &so, &co);
+  const bool kin = MODEL == MPCB_MODEL_KINEMATIC4;
+  const double vx = kin ? y[3] * c : y[3] * c - y[MODEL == MPCB_MODEL_KINEMATIC4 ? 3 : 4] * s;
+  const double vy = kin ? y[3] * s : y[3] * s + y[MODEL == MPCB_MODEL_KINEMATIC4 ? 3 : 4] * c;
+  const double dvx = vx - vo * co, dvy = vy - vo * so;
+  const double xs = d.safe_x0 / 2.0 + dvx * dvx / (2.0 * d.safe_ax);
+  const double ys = d.safe_y0 / 2.0 + dvy * dvy / (2.0 * d.safe_ay);
+  const double dx = y[0] - xo, dy = y[1] - yo;
+  const double g = 1.0 - dx * dx / (xs * xs) - dy * dy / (ys * ys);
+  if (gy) {
+    const double gvx = 2.0 * dx * dx / (xs * xs * xs) * dvx / d.safe_ax;
+    const double gvy = 2.0 * dy * dy / (ys * ys * ys) * dvy / d.safe_ay;
+    gy[0] -= w * 2.0 * dx / (xs * xs);
+    gy[1] -= w * 2.0 * dy / (ys * ys);
+    gy[2] += w * (gvx * (-vy) + gvy * vx);
+    gy[3] += w * (gvx * c + gvy * s);
+    if constexpr (MODEL != MPCB_MODEL_KINEMATIC4) gy[4] += w * (-gvx * s + gvy * c);
+  }
+  return g;
+}
+
 // Per-instance extras for the optional cost terms.
 struct Extras {
   const double* obs;         // [n_obs,5] of this instance or null
@@ -345,13 +374,30 @@ MPCB_DEV double stage_cost(const KDesc& d, const RoadView& r, const Extras& ex, 
     }
   }
   if (d.bounded && ex.lam && ex.Sig) {
+    const int R = d.rows;
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
       double gi = y[i] * y[i] - d.g_off[i];
       double yh;
-      L += alm_row(gi, ex.lam[(int64_t)(n * NX + i) * ex.lam_stride], ex.Sig[(int64_t)(n * NX + i) * ex.sig_stride],
+      L += alm_row(gi, ex.lam[(int64_t)(n * R + i) * ex.lam_stride], ex.Sig[(int64_t)(n * R + i) * ex.sig_stride],
                    d.D_lo[i], d.D_hi[i], &yh, nullptr);
       if (GRAD) gy[i] += 2.0 * yh * y[i];
+    }
+    if ((d.flags & MPCB_FLAG_SAFE_DIST) && ex.obs) {  // one ellipse row per obstacle, D = (-inf, 0]
+      const double t = (double)(n + 1) * d.Ts;
+      const double ninf = __longlong_as_double(0xfff0000000000000LL);
+      for (int o = 0; o < d.n_obs; ++o) {
+        const double* ob = ex.obs + MPCB_OBS_DIM * o;
+        double so, co;
+        sincos(ob[2], &so, &co);
+        const double sdist = ob[3] * t + 0.5 * ob[4] * t * t;  // event_triggered.py:26
+        const double xo = ob[0] + sdist * co, yo = ob[1] + sdist * so, vo = ob[3] + ob[4] * t;
+        const double gi = safe_dist_row<MODEL>(d, y, xo, yo, ob[2], vo, 0.0, nullptr);
+        double yh;
+        L += alm_row(gi, ex.lam[(int64_t)(n * R + NX + o) * ex.lam_stride], ex.Sig[(int64_t)(n * R + NX + o) * ex.sig_stride],
+                     ninf, 0.0, &yh, nullptr);
+        if (GRAD) safe_dist_row<MODEL>(d, y, xo, yo, ob[2], vo, yh, gy);
+      }
     }
   }
   return L;

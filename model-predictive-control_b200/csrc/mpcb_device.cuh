@@ -28,6 +28,8 @@ struct KDesc {
   double lane_a, lane_y_t, lane_b, lane_y_br, lane_y_bl;
   double obs_Af, obs_b, obs_sx, obs_sy, obs_adiv;
   double g_off[6], D_lo[6], D_hi[6];
+  int rows;  // rows of g per stage: nx state rows (main.py:46-51) + n_obs safe-distance ellipses (MPCB_FLAG_SAFE_DIST); m = rows N
+  double safe_x0, safe_y0, safe_ax, safe_ay;  // dpf_test.py:6
 };
 
 // Vehicle constants staged once per CTA in shared memory (runtime parameter p[22], main.py:119).

@@ -565,7 +565,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         if (d.bounded) {  // clamp multipliers to ±M, 0 on infinite sides
           if (l == 0) {
             for (int r = 0; r < m; ++r) {
-              double lo = isinf(d.D_lo[r % NX]) ? 0.0 : -sp.M, hi = isinf(d.D_hi[r % NX]) ? 0.0 : sp.M;
+              const int ri = r % d.rows;  // state rows: their box; ellipse rows (MPCB_FLAG_SAFE_DIST): D = (-inf, 0]
+              double lo = ri < NX ? (isinf(d.D_lo[ri]) ? 0.0 : -sp.M) : 0.0, hi = ri < NX ? (isinf(d.D_hi[ri]) ? 0.0 : sp.M) : sp.M;
               double lv = a.lam[b * m + r];
               a.lam[b * m + r] = lv < lo ? lo : (lv > hi ? hi : lv);
             }
@@ -967,24 +968,40 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         }
         state = ST_ALM_UPDATE;
       } else if (state == ST_ALM_V) {
-        // err_z = g(x̂) − Π_D(ζ), λ ← ŷ(x̂)
+        // err_z = g(x̂) − Π_D(ζ), λ ← ŷ(x̂); row r = (stage, state component | obstacle)
         Vec STt = WL(M.ST, 0);
+        auto row_at = [&](int r, double* yh, double* ez) {
+          const int R = d.rows, nn = r / R, ri = r - nn * R;
+          double g, lo, hi;
+          if (ri < NX) {
+            const double y = STt(nn * NX + ri);
+            g = y * y - d.g_off[ri]; lo = d.D_lo[ri]; hi = d.D_hi[ri];
+          } else {
+            double yy[NX];
+#pragma unroll
+            for (int j = 0; j < NX; ++j) yy[j] = STt(nn * NX + j);
+            const double* ob = a.obs + (b * d.n_obs + (ri - NX)) * MPCB_OBS_DIM;
+            const double t = (double)(nn + 1) * d.Ts;
+            double so, co;
+            sincos(ob[2], &so, &co);
+            const double sdist = ob[3] * t + 0.5 * ob[4] * t * t;  // event_triggered.py:26
+            g = safe_dist_row<MODEL>(d, yy, ob[0] + sdist * co, ob[1] + sdist * so, ob[2], ob[3] + ob[4] * t, 0.0, nullptr);
+            lo = __longlong_as_double(0xfff0000000000000LL); hi = 0.0;
+          }
+          alm_row(g, a.lam[b * m + r], TR(T.SIG, r), lo, hi, yh, ez);
+        };
         norm_e2 = 0.0;
         for (int r = 0; r < m; ++r) {
-          int i = r % NX;
-          double y = STt(r);
           double yh, ez;
-          alm_row(y * y - d.g_off[i], a.lam[b * m + r], TR(T.SIG, r), d.D_lo[i], d.D_hi[i], &yh, &ez);
+          row_at(r, &yh, &ez);
           TR(T.E2, r) = ez;
           norm_e2 = fmax(norm_e2, fabs(ez));
         }
         tsync();  // every lane has read the old multipliers before lane 0 overwrites them
         if (l == 0) {
           for (int r = 0; r < m; ++r) {
-            int i = r % NX;
-            double y = STt(r);
             double yh, ez;
-            alm_row(y * y - d.g_off[i], a.lam[b * m + r], TR(T.SIG, r), d.D_lo[i], d.D_hi[i], &yh, &ez);
+            row_at(r, &yh, &ez);
             a.lam[b * m + r] = yh;
           }
         }

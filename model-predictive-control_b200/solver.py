@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _ffi
-from ._ffi import (FLAG_BOUNDED_D, FLAG_EXACT, FLAG_LANE, FLAG_OBST, MODEL_KINEMATIC4, MODEL_PACEJKA6, ROAD_BEZIER,
+from ._ffi import (FLAG_BOUNDED_D, FLAG_EXACT, FLAG_LANE, FLAG_OBST, FLAG_SAFE_DIST, MODEL_KINEMATIC4, MODEL_PACEJKA6, ROAD_BEZIER,
                    ROAD_PER_INSTANCE, ROAD_SHARED, ROAD_TABLE)
 
 
@@ -75,7 +75,9 @@ class BatchedMpc:
         self.desc = d
         self.N, self.S, self.model_id = N, S, model_id
         self.nx = 4 if model_id == MODEL_KINEMATIC4 else 6
-        self.n, self.m = 2 * N, self.nx * N
+        # rows of g per stage: the nx state rows (main.py:46-51) + one safe-distance ellipse per obstacle (MPCB_FLAG_SAFE_DIST)
+        self.rows = self.nx + (n_obs if flags & FLAG_SAFE_DIST else 0)
+        self.n, self.m = 2 * N, self.rows * N
         self._h = C.c_void_p()
         with torch.cuda.device(self.device):
             _ffi.check(self._lib.mpcb_create(C.byref(d), C.byref(self._h)), None, "mpcb_create")

@@ -66,6 +66,7 @@ const double* road_of(const MpcProblemDesc* d, const double* road, const int32_t
 }
 
 bool is_bounded(const MpcProblemDesc* d) {
+  if ((d->flags & MPCB_FLAG_SAFE_DIST) && d->n_obs > 0) return true;
   if (!(d->flags & MPCB_FLAG_BOUNDED_D)) return false;
   for (int i = 0; i < nx_of(d->model_id); ++i)
     if (!std::isinf(d->D_lower[i]) || !std::isinf(d->D_upper[i])) return true;
@@ -124,6 +125,9 @@ void orc_bezier_control_points(double i, double h, double W, double theta, doubl
   bezier_control_points(i, h, W, theta, l, Lf, v0, v1, D1, P12, tca);
 }
 
+void orc_safe_distances(const MpcProblemDesc* d, const double* Xe, const double* Xo, double* out2) {  // dpf_test.py:57-64
+  safe_distances(*d, Xe[2], Xe[3], Xo[2], Xo[3], &out2[0], &out2[1]);
+}
 double orc_u_trgl(double y, double y_t, double a) { return u_trgl(y, y_t, a); }
 double orc_u_rbd(double y, double y_br, double y_bl, double b) { return u_rbd(y, y_br, y_bl, b); }
 double orc_dnf(double x, double y, double phi, double v, int n_obs, const double* xo, const double* yo,
@@ -170,7 +174,7 @@ void orc_value_grad_batch(const MpcProblemDesc* d, int64_t B, const double* x0, 
     for (int64_t b = 0; b < B; ++b) {
       const double* r = road_of(d, road, road_idx, b, tmp);
       Instance<double> I = make_instance<double>(d, p, r, obs ? obs + b * d->n_obs * MPCB_OBS_DIM : nullptr,
-                                                 lam ? lam + b * nx * N : nullptr, Sig ? Sig + b * nx * N : nullptr);
+                                                 lam ? lam + b * rows_of(*d) * N : nullptr, Sig ? Sig + b * rows_of(*d) * N : nullptr);
       cost[b] = value_grad(I, x0 + b * nx, U + b * 2 * N, grad + b * 2 * N);
     }
   }
@@ -237,7 +241,7 @@ void orc_solve_batch(const MpcProblemDesc* d, const MpcSolverParams* sp, int64_t
   const bool bounded = is_bounded(d);
 #pragma omp parallel num_threads(threads)
   {
-    std::vector<double> tmp, lam_local(size_t(nx) * N);
+    std::vector<double> tmp, lam_local(size_t(rows_of(*d)) * N);
 #pragma omp for schedule(dynamic, 1)
     for (int64_t b = 0; b < B; ++b) {
       double t0 = omp_get_wtime();
@@ -248,9 +252,9 @@ void orc_solve_batch(const MpcProblemDesc* d, const MpcSolverParams* sp, int64_t
       P.lb = lb;
       P.ub = ub;
       P.n = 2 * N;
-      P.m = nx * N;
+      P.m = rows_of(*d) * N;
       P.bounded = bounded;
-      double* lm = lam ? lam + b * nx * N : lam_local.data();
+      double* lm = lam ? lam + b * rows_of(*d) * N : lam_local.data();
       if (!lam) std::fill(lam_local.begin(), lam_local.end(), 0.0);
       SolveResult R = alm_solve(P, *sp, U + b * 2 * N, lm);
       if (status) status[b] = R.status;

@@ -143,6 +143,19 @@ def bezier_control_points(i, h, W, theta, l, Lf, v0, v1, D1):
     return P.reshape(2, 6), tca.value
 
 
+def safe_distances(X_e, X_obs, desc=None):
+    """dpf_test.py:57-64 get_safe_distances(X_e, X_obs) -> (x_s, y_s)."""
+    d = default_desc() if desc is None else desc
+    out = np.zeros(2)
+    lib().orc_safe_distances(C.byref(d), _p(f64(X_e)), _p(f64(X_obs)), _p(out))
+    return out[0], out[1]
+
+
+def rows_per_stage(desc):
+    nx = 4 if desc.model_id == 1 else 6
+    return nx + (desc.n_obs if desc.flags & 16 else 0)
+
+
 def u_trgl(y, y_t, a=0.5):
     return lib().orc_u_trgl(y, y_t, a)
 
@@ -200,7 +213,7 @@ def solve(desc, sp, x0, road, U, lam=None, p=DEFAULT_P, road_idx=None, obs=None,
     x0 = f64(x0).reshape(-1, nx)
     B, N = x0.shape[0], desc.N
     U = f64(U).reshape(B, 2 * N).copy()
-    lam = None if lam is None else f64(lam).reshape(B, nx * N).copy()
+    lam = None if lam is None else f64(lam).reshape(B, rows_per_stage(desc) * N).copy()
     road, p = f64(road), f64(p)
     obs = None if obs is None else f64(obs)
     road_idx = _i32(road_idx)
@@ -278,6 +291,7 @@ def default_desc(model_id=0, N=12, S=100):
         d.g_offset[i] = v
         d.D_lower[i] = -np.inf
         d.D_upper[i] = np.inf
+    d.safe_x0, d.safe_y0, d.safe_ax_max, d.safe_ay_max = 5.0, 3.0, 3.0, 1.0   # dpf_test.py:6
     return d
 
 

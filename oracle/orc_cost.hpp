@@ -186,6 +186,48 @@ inline T alm_row(const T& g, const T& lam, const T& Sig, double lo, double hi, T
   return T(0.5) * Sig * dz * dz;
 }
 
+// Rows of g per stage: the nx state rows of main.py:46-51, plus one safe-distance ellipse per obstacle with
+// MPCB_FLAG_SAFE_DIST.
+inline int rows_of(const MpcProblemDesc& d) {
+  return nx_of(d.model_id) + ((d.flags & MPCB_FLAG_SAFE_DIST) ? d.n_obs : 0);
+}
+
+// dpf_test.py:57-64 get_safe_distances: X = (x, y, v_x, v_y) in the world frame.
+template <class T>
+inline void safe_distances(const MpcProblemDesc& d, const T& vxe, const T& vye, const T& vxo, const T& vyo, T* xs, T* ys) {
+  *xs = T(d.safe_x0) / T(2) + (vxe - vxo) * (vxe - vxo) / (T(2) * T(d.safe_ax_max));
+  *ys = T(d.safe_y0) / T(2) + (vye - vyo) * (vye - vyo) / (T(2) * T(d.safe_ay_max));
+}
+
+// The ellipse of semi-axes (x_s, y_s) around an obstacle as a constraint row: g = 1 - (dx/x_s)^2 - (dy/y_s)^2 <= 0.
+// The ego's world-frame velocity is (v cos phi, v sin phi) for Kinematic-4 and R(phi) (vx, vy) for Pacejka-6; gy
+// (nullable, nx entries, ACCUMULATED with weight w) receives w * dg/dy.
+template <class T>
+inline T safe_dist_row(const MpcProblemDesc& d, const T* y, const T& xo, const T& yo, const T& po, const T& vo, const T& w, T* gy) {
+  const bool kin = d.model_id == MPCB_MODEL_KINEMATIC4;
+  T s = sin(y[2]), c = cos(y[2]);
+  T vx = kin ? y[3] * c : y[3] * c - y[4] * s, vy = kin ? y[3] * s : y[3] * s + y[4] * c;
+  T vxo = vo * cos(po), vyo = vo * sin(po);
+  T xs, ys;
+  safe_distances(d, vx, vy, vxo, vyo, &xs, &ys);
+  T dx = y[0] - xo, dy = y[1] - yo;
+  T g = T(1) - dx * dx / (xs * xs) - dy * dy / (ys * ys);
+  if (gy) {
+    T gvx = T(2) * dx * dx / (xs * xs * xs) * (vx - vxo) / T(d.safe_ax_max);   // dg/dv_x through x_s
+    T gvy = T(2) * dy * dy / (ys * ys * ys) * (vy - vyo) / T(d.safe_ay_max);
+    gy[0] = gy[0] - w * T(2) * dx / (xs * xs);
+    gy[1] = gy[1] - w * T(2) * dy / (ys * ys);
+    gy[2] = gy[2] + w * (gvx * (-vy) + gvy * vx);                               // d(v_x, v_y)/dphi = (-v_y, v_x)
+    if (kin) {
+      gy[3] = gy[3] + w * (gvx * c + gvy * s);
+    } else {
+      gy[3] = gy[3] + w * (gvx * c + gvy * s);
+      gy[4] = gy[4] + w * (-gvx * s + gvy * c);
+    }
+  }
+  return g;
+}
+
 // Stage cost L(y_{n+1}, u_n) of car_dynamics.py:230-258 plus the optional terms; gy/gu (nullable)
 // receive dL/dy, dL/du with the selection indices held constant and d wrap/da = 1.
 template <class T>
@@ -239,12 +281,24 @@ inline T stage_cost(const Instance<T>& I, int n, const T* y, const T* u, int* id
       if (gy) for (int i = 0; i < 4; ++i) gy[i] = gy[i] + g4[i];
     }
   }
+  const int R = rows_of(d);
   if ((d.flags & MPCB_FLAG_BOUNDED_D) && I.lam && I.Sig) {
     for (int i = 0; i < nx; ++i) {
       T g = y[i] * y[i] - T(d.g_offset[i]);  // main.py:46-51
       T yh;
-      L = L + alm_row(g, I.lam[n * nx + i], I.Sig[n * nx + i], d.D_lower[i], d.D_upper[i], &yh, (T*)nullptr);
+      L = L + alm_row(g, I.lam[n * R + i], I.Sig[n * R + i], d.D_lower[i], d.D_upper[i], &yh, (T*)nullptr);
       if (gy) gy[i] = gy[i] + yh * T(2) * y[i];
+    }
+  }
+  if ((d.flags & MPCB_FLAG_SAFE_DIST) && I.obs && I.lam && I.Sig) {
+    T t = T(double(n + 1)) * T(d.Ts);
+    for (int o = 0; o < d.n_obs; ++o) {
+      T xo, yo, po, vo;
+      obstacle_at(I.obs + MPCB_OBS_DIM * o, t, &xo, &yo, &po, &vo);
+      T g = safe_dist_row(d, y, xo, yo, po, vo, T(0), (T*)nullptr);
+      T yh;
+      L = L + alm_row(g, I.lam[n * R + nx + o], I.Sig[n * R + nx + o], -INFINITY, 0.0, &yh, (T*)nullptr);
+      if (gy) safe_dist_row(d, y, xo, yo, po, vo, yh, gy);
     }
   }
   return L;

@@ -33,17 +33,28 @@ struct Problem {
   // err_z = g(x) - Pi_D(zeta(x)), yhat(x)   (Appendix A 3b); zero when D is unbounded.
   void err_z_yhat(const double* x, double* err_z, double* yhat) {
     const MpcProblemDesc& d = *I.d;
-    const int nx = I.M.nx();
+    const int nx = I.M.nx(), R = rows_of(d);
     if (!bounded) { for (int i = 0; i < m; ++i) { err_z[i] = 0; yhat[i] = 0; } return; }
     std::vector<double> st(size_t(d.N) * nx);
     rollout(I, x0, x, st.data(), (int*)nullptr, (double*)nullptr);
-    for (int nn = 0; nn < d.N; ++nn)
+    for (int nn = 0; nn < d.N; ++nn) {
       for (int i = 0; i < nx; ++i) {
         double y = st[nn * nx + i];
         double g = y * y - d.g_offset[i];
-        alm_row(g, I.lam[nn * nx + i], I.Sig[nn * nx + i], d.D_lower[i], d.D_upper[i], &yhat[nn * nx + i],
-                &err_z[nn * nx + i]);
+        const bool on = (d.flags & MPCB_FLAG_BOUNDED_D) != 0;   // state rows are live only with MPCB_FLAG_BOUNDED_D
+        alm_row(g, I.lam[nn * R + i], I.Sig[nn * R + i], on ? d.D_lower[i] : -INFINITY, on ? d.D_upper[i] : INFINITY,
+                &yhat[nn * R + i], &err_z[nn * R + i]);
       }
+      if (d.flags & MPCB_FLAG_SAFE_DIST) {
+        const double t = double(nn + 1) * d.Ts;
+        for (int o = 0; o < d.n_obs; ++o) {
+          double xo, yo, po, vo;
+          obstacle_at(I.obs + MPCB_OBS_DIM * o, t, &xo, &yo, &po, &vo);
+          double g = safe_dist_row(d, &st[nn * nx], xo, yo, po, vo, 0.0, (double*)nullptr);
+          alm_row(g, I.lam[nn * R + nx + o], I.Sig[nn * R + nx + o], -INFINITY, 0.0, &yhat[nn * R + nx + o], &err_z[nn * R + nx + o]);
+        }
+      }
+    }
   }
 };
 
@@ -304,8 +315,10 @@ inline SolveResult alm_solve(Problem& P, const MpcSolverParams& sp, double* U, d
   for (int i = 0;; ++i) {
     if (P.bounded)
       for (int r = 0; r < m; ++r) {  // clamp y to +-M respecting infinite D sides
-        double lo = std::isinf(d.D_lower[r % nx]) ? 0.0 : -sp.M;
-        double hi = std::isinf(d.D_upper[r % nx]) ? 0.0 : sp.M;
+        const int R = rows_of(d), i = r % R;
+        const bool state_on = i < nx && (d.flags & MPCB_FLAG_BOUNDED_D);
+        double lo = i < nx ? ((!state_on || std::isinf(d.D_lower[i])) ? 0.0 : -sp.M) : 0.0;   // ellipse rows: D = (-inf, 0]
+        double hi = i < nx ? ((!state_on || std::isinf(d.D_upper[i])) ? 0.0 : sp.M) : sp.M;
         lam[r] = lam[r] < lo ? lo : (lam[r] > hi ? hi : lam[r]);
       }
     P.I.lam = P.bounded ? lam : nullptr;

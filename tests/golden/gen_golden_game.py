@@ -54,6 +54,15 @@ def main():
             cars.append(gt.Car(name=f"Car{k + 1}", x=float(rng.uniform(-60, 90)), v=float(rng.choice([0.0, rng.uniform(0, 25)])),
                                lane=int(rng.integers(1, 3))))
         out["cases"].append(case(gt, ego, np.array(cars)))
+    # dpf_test.py:57-64 get_safe_distances (its module-level grid sweep runs at import: 0.4 s)
+    import dpf_test
+    sd = []
+    for _ in range(40):
+        Xe = [float(v) for v in rng.uniform(-20, 20, 4)]
+        Xo = [float(v) for v in rng.uniform(-20, 20, 4)]
+        xs, ys = dpf_test.get_safe_distances(Xe, Xo)
+        sd.append({"X_e": Xe, "X_obs": Xo, "x_s": float(xs), "y_s": float(ys)})
+    out["safe_distances"] = {"x_0": dpf_test.x_0, "y_0": dpf_test.y_0, "a_x_max": dpf_test.a_x_max, "a_y_max": dpf_test.a_y_max, "cases": sd}
     c0 = gt.Car()
     out["car_defaults"] = {"L": c0.L, "W": c0.W, "l": c0.l, "theta_max": float(c0.θ_max), "tlc": c0.tlc, "td": c0.td, "ti": c0.ti,
                            "tau": c0.τ, "a_max": c0.a_max, "h": c0.h, "Lf": c0.Lf}

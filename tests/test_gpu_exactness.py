@@ -335,3 +335,113 @@ def test_graph_driven_loop_equals_host_loop(mp, problem, monkeypatch):
               f"{t_call['host'] * 1e3:.1f} of {t_total['host'] * 1e3:.1f} ms)")
         assert t_call["graph"] < 0.25 * t_total["graph"]       # asynchronous on the caller's stream
         assert t_call["host"] > 0.9 * t_total["host"]          # the host loop blocks
+
+
+# ------------------------------------------------------------------ 7. safe-distance ellipse constraints
+def _ellipse_problem(mp, orc, B, N, seed, n_obs=1):
+    """Kinematic-4 lane change on a Bezier road past a slower car, the obstacle as the `get_safe_distances` ellipse
+    CONSTRAINT (dpf_test.py:57-64, MPCB_FLAG_SAFE_DIST) instead of the `dnf` potential."""
+    from mpcb200 import workloads as wl
+    lc = wl.lane_change_batch(B, N, 100, seed=seed, n_obs=n_obs)
+    flags = mp.FLAG_LANE | mp.FLAG_SAFE_DIST
+    prob = mp.BatchedMpc(N=N, S=100, model_id=1, road_mode=mp.ROAD_BEZIER, flags=flags, n_obs=n_obs, v_ref=20.0)
+    d = orc.default_desc(1, N, 100)
+    d.road_mode, d.flags, d.n_obs, d.v_ref = 3, flags, n_obs, 20.0
+    return prob, d, lc
+
+
+@pytest.mark.parametrize("model", [1, 0])
+def test_ellipse_rows_value_and_gradient_parity(mp, orc, model):
+    from mpcb200 import workloads as wl
+    B, N, n_obs = 64, 20, 2
+    rng = np.random.default_rng(5)
+    if model == 1:
+        prob, d, lc = _ellipse_problem(mp, orc, B, N, seed=7, n_obs=n_obs)
+        x0, road, obs, ridx = lc["x0"], lc["ctrl"], lc["obs"], None
+    else:
+        w = wl.tracking_batch(B, N, 100, seed=7)
+        flags = mp.FLAG_SAFE_DIST | mp.FLAG_BOUNDED_D
+        Dup = [np.inf, np.inf, np.inf, -1.0, np.inf, np.inf]
+        prob = mp.BatchedMpc(N=N, S=100, road_mode=mp.ROAD_TABLE, n_roads=2, flags=flags, n_obs=n_obs, D_upper=Dup)
+        d = _orc_desc(orc, 0, N, 1, 2, flags=flags, n_obs=n_obs, D_upper=Dup)
+        x0, road, ridx = w["x0"], w["road"], w["road_idx"]
+        obs = np.zeros((B, n_obs, 5))
+        obs[:, :, 0] = x0[:, None, 0] + rng.uniform(0.3, 1.5, (B, n_obs))
+        obs[:, :, 1] = x0[:, None, 1] + rng.uniform(-0.3, 0.3, (B, n_obs))
+        obs[:, :, 3] = rng.uniform(0.2, 0.8, (B, n_obs))
+    R = prob.rows
+    assert R == prob.nx + n_obs and prob.m == R * N
+    U = np.zeros((B, 2 * N))
+    U[:, 0::2], U[:, 1::2] = rng.uniform(0, 1, (B, N)), rng.uniform(-0.1, 0.1, (B, N))
+    lam, Sig = rng.uniform(0, 2, (B, R * N)), np.full((B, R * N), 10.0)
+    c, g = prob.value_grad(x0, U, road, road_idx=ridx, obs=obs, lam=lam, Sigma=Sig)
+    c_r, g_r = orc.value_grad(d, x0, U, road, road_idx=ridx, obs=obs, lam=lam, Sigma=Sig)
+    np.testing.assert_allclose(c.cpu().numpy(), c_r, rtol=1e-9)
+    scale = np.abs(g_r).max(axis=1, keepdims=True)
+    assert (np.abs(g.cpu().numpy() - g_r) / scale).max() < 1e-7
+
+
+def test_ellipse_constrained_solve_meets_the_oracle(mp, orc, monkeypatch):
+    """ALM solve with the ellipse rows against the oracle's cold solve: same statuses, the GPU's answers satisfy the
+    constraint to the ALM's delta by the oracle's own rollout, multipliers and U* within the spread of the other solves;
+    and the answer does not depend on the loop (graph / host), the execution mode's speculation width or the EXACT switch."""
+    import torch
+    B, N = 96, 20
+    prob, d, lc = _ellipse_problem(mp, orc, B, N, seed=11)
+    R = prob.rows
+    # put every obstacle where the uncontrolled rollout (U0) ends, in the ego's lane and slower, so that its ellipse
+    # overlaps the end of the horizon and the solver has to brake or swerve
+    end = orc.rollout(d, lc["x0"], lc["U0"], lc["ctrl"], obs=lc["obs"])[0][:, -1]
+    rng = np.random.default_rng(11)
+    v_obs = end[:, 3] * rng.uniform(0.5, 0.9, B)
+    xs_end = 2.5 + (end[:, 3] - v_obs) ** 2 / 6.0
+    lc["obs"][:, 0, 0] = end[:, 0] + rng.uniform(0.5, 0.9, B) * xs_end - v_obs * N * 0.05   # position at t = 0
+    lc["obs"][:, 0, 1] = end[:, 1] + rng.uniform(-0.3, 0.3, B)
+    lc["obs"][:, 0, 2] = 0.0
+    lc["obs"][:, 0, 3] = v_obs
+    lc["obs"][:, 0, 4] = 0.0
+    U, lam, st = prob.solve(lc["x0"], lc["ctrl"], lc["U0"].copy(), lam=np.zeros((B, R * N)), obs=lc["obs"])
+    r = orc.solve(d, orc.default_solver_params(N), lc["x0"], lc["ctrl"], lc["U0"], lam=np.zeros((B, R * N)), obs=lc["obs"])
+    sg = st.status.cpu().numpy()
+    agree = sg == r["status"]
+    ok = (sg == 1) & (r["status"] == 1)
+    Un, lamn = U.cpu().numpy(), lam.cpu().numpy()
+    # constraint satisfaction of the GPU's answers by the oracle: err_z of the ellipse rows <= delta
+    states = orc.rollout(d, lc["x0"], Un, lc["ctrl"], obs=lc["obs"])[0]
+    t = (np.arange(N) + 1) * 0.05
+    ob = lc["obs"][:, 0]
+    xo = ob[:, None, 0] + (ob[:, None, 3] * t + 0.5 * ob[:, None, 4] * t * t) * np.cos(ob[:, None, 2])
+    yo = ob[:, None, 1] + (ob[:, None, 3] * t + 0.5 * ob[:, None, 4] * t * t) * np.sin(ob[:, None, 2])
+    vo = ob[:, None, 3] + ob[:, None, 4] * t
+    vx, vy = states[:, :, 3] * np.cos(states[:, :, 2]), states[:, :, 3] * np.sin(states[:, :, 2])
+    xs = 2.5 + (vx - vo * np.cos(ob[:, None, 2])) ** 2 / 6.0
+    ys = 1.5 + (vy - vo * np.sin(ob[:, None, 2])) ** 2 / 2.0
+    gval = 1.0 - ((states[:, :, 0] - xo) / xs) ** 2 - ((states[:, :, 1] - yo) / ys) ** 2
+    viol = np.maximum(gval, 0.0).max(axis=1)
+    active = (lamn.reshape(B, N, R)[:, :, prob.nx:] > 0).any(axis=(1, 2))
+    err = np.abs(Un - r["U"]).max(axis=1)
+    print(f"ellipse rows: statuses GPU {np.bincount(sg)} oracle {np.bincount(r['status'])}, equal {agree.mean():.3f}; constraint active "
+          f"in {active[ok].mean():.2f}; violation max {viol[ok].max():.2e}; |dU| median {np.median(err[ok]):.1e} p95 {np.quantile(err[ok], .95):.1e}")
+    gap = np.abs(st.psi.cpu().numpy() - r["psi"])[ok] / (1.0 + np.abs(r["psi"][ok]))
+    lerr = (np.abs(lamn - r["lam"]).max(axis=1) / (1.0 + np.abs(r["lam"]).max(axis=1)))[ok]
+    print(f"   psi rel gap median {np.median(gap):.1e} p95 {np.quantile(gap, .95):.1e}; multiplier rel err median {np.median(lerr):.1e}; "
+          f"outer iterations GPU median {np.median(st.outer_iterations.cpu().numpy()[ok]):.0f} oracle {np.median(r['outer'][ok]):.0f}")
+    assert agree.mean() >= 0.9 and ok.mean() > 0.5
+    assert active[ok].mean() > 0.2                          # the constraint is exercised
+    assert (viol[ok] <= 1e-4 * (1 + 1e-6)).all()            # feasible to the ALM's delta, by the oracle's rollout
+    assert np.median(gap) < 1e-4                            # the same optimum value
+    # bit-equality across the loop, the window width and the EXACT switch for this problem class
+    ref = (U, st)
+    for env in ({"MPCB_LOOP": "host"}, {"MPCB_SPECW": "1"}, {"MPCB_EXACT": "1"}, {"MPCB_MODE": "persistent", "MPCB_EXACT": "1"}):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        p2, _, _ = _ellipse_problem(mp, orc, B, N, seed=11)
+        U2, lam2, st2 = p2.solve(lc["x0"], lc["ctrl"], lc["U0"].copy(), lam=np.zeros((B, R * N)), obs=lc["obs"])
+        for k in env:
+            monkeypatch.delenv(k)
+        if env.get("MPCB_MODE") == "persistent":   # the two modes use different psi-only kernels: compare to tolerance
+            same = (st2.inner_iterations == st.inner_iterations).cpu().numpy()
+            assert same.mean() > 0.9 and float((U2 - U).abs().max(dim=1).values.cpu().numpy()[same].max()) < 1e-6
+        else:
+            _assert_same_solution(ref, (U2, st2), f"ellipse rows: default vs {env}")
+            assert torch.equal(lam, lam2)

@@ -118,3 +118,49 @@ def test_scipy_and_oracle_panoc_reach_the_same_minimum_on_a_batch(orc):
     assert (o["status"] == 1).all()
     assert np.median(np.abs(gap)) < 1e-9
     assert np.mean(dU < 1e-5) >= 0.75
+
+
+def test_safe_distances_match_reference_and_ellipse_rows_have_the_right_gradient(orc):
+    """dpf_test.py:57-64 `get_safe_distances` against vectors produced by the reference's own code, and the ellipse
+    constraint rows built from it (MPCB_FLAG_SAFE_DIST: g = 1 - (dx/x_s)^2 - (dy/y_s)^2, through the ALM terms of psi)
+    against central differences — both vehicle models, the state rows of main.py:46-51 active next to them."""
+    import json
+    import os
+    from mpcb200 import workloads as wl
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_game_theory.json")))
+    sd = g["safe_distances"]
+    assert (sd["x_0"], sd["y_0"], sd["a_x_max"], sd["a_y_max"]) == (5, 3, 3, 1)
+    for c in sd["cases"]:
+        assert orc.safe_distances(c["X_e"], c["X_obs"]) == (c["x_s"], c["y_s"])
+    for model, N in ((1, 12), (0, 12)):
+        B, n_obs = 12, 2
+        d = orc.default_desc(model, N, S)
+        rng = np.random.default_rng(3)
+        if model == 1:
+            lc = wl.lane_change_batch(B, N, S, seed=7, n_obs=n_obs)
+            d.road_mode, d.flags, d.n_obs, d.v_ref = 3, 2 | 16, n_obs, 20.0
+            x0, road, obs, ridx = lc["x0"], lc["ctrl"], lc["obs"], None
+        else:
+            w = wl.tracking_batch(B, N, S, seed=7)
+            d.road_mode, d.n_roads, d.flags, d.n_obs = 1, 2, 16 | 4, n_obs
+            d.D_upper[3] = -1.0
+            x0, road, ridx = w["x0"], w["road"], w["road_idx"]
+            obs = np.zeros((B, n_obs, 5))
+            obs[:, :, 0] = x0[:, None, 0] + rng.uniform(0.3, 1.5, (B, n_obs))
+            obs[:, :, 1] = x0[:, None, 1] + rng.uniform(-0.3, 0.3, (B, n_obs))
+            obs[:, :, 3] = rng.uniform(0.2, 0.8, (B, n_obs))
+        R = orc.rows_per_stage(d)
+        assert R == (4 if model == 1 else 6) + n_obs
+        U = np.zeros((B, 2 * N))
+        U[:, 0::2], U[:, 1::2] = rng.uniform(0, 1, (B, N)), rng.uniform(-0.1, 0.1, (B, N))
+        lam, Sig = rng.uniform(0, 2, (B, R * N)), np.full((B, R * N), 10.0)
+        kw = dict(road_idx=ridx, obs=obs, lam=lam, Sigma=Sig)
+        _, gr = orc.value_grad(d, x0, U, road, **kw)
+        h, fd = 1e-6, np.zeros_like(gr)
+        for i in range(2 * N):
+            Up, Um = U.copy(), U.copy()
+            Up[:, i] += h
+            Um[:, i] -= h
+            fd[:, i] = (orc.value_grad(d, x0, Up, road, **kw)[0] - orc.value_grad(d, x0, Um, road, **kw)[0]) / (2 * h)
+        err = np.abs(fd - gr).max(axis=1) / np.abs(gr).max(axis=1)
+        assert np.median(err) < 1e-7 and err.max() < 1e-5, (model, err.max())
