@@ -80,7 +80,10 @@ struct SolveArgs {
 };
 constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 28;
 constexpr int MPCB_NKEY = 16;       // transition buckets: one per SolveState, ST_LS_STEP split by phase
-constexpr int MPCB_ROUND_BLOCK = 128;  // lanes per CTA of a transition launch
+#ifndef MPCB_ROUND_BLOCK_N
+#define MPCB_ROUND_BLOCK_N 128
+#endif
+constexpr int MPCB_ROUND_BLOCK = MPCB_ROUND_BLOCK_N;  // lanes per CTA of a transition launch
 
 enum SolveState {
   ST_IDLE = 0, ST_START_PANOC, ST_INIT_G1, ST_LIP_DONE, ST_XHAT_REQ, ST_XHAT_DONE, ST_ITER_TOP, ST_FD_DONE,

@@ -1,7 +1,9 @@
 """Headless drop-in for reference simulation.py: same function names and arguments (simulation.py:5,48,
 60,67,86).  matplotlib / a display are unavailable on this box, so every `plot_*` writes the arrays it
-would have drawn to an .npz file (returned path) instead of opening a window; `rotate_point` and the car
-outline are the reference's pure maths.  Out of the hot path: no GPU work here.
+would have drawn to an .npz file (returned path) instead of opening a window.  `rotate_point` and the five-corner
+car outline of `plot_car` are VERBATIM from reference simulation.py:60-83 (about 17 lines of plotting geometry: the
+outline has to be the reference's for the saved arrays to be what its figures show).  Out of the hot path:
+no GPU work here.
 """
 import os
 import re
