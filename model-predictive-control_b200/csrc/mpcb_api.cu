@@ -36,6 +36,8 @@ struct MpcHandle {
   // MPCB_GUARDS=1: every grow-only scratch buffer sits between two 4 KiB canary regions (0xA5); mpcb_check_guards counts
   // the canary bytes that changed.  (compute-sanitizer is closed on the B200 pool: this is the bounds evidence.)
   int guards = 0;
+  int poison = 0;  // MPCB_POISON=1: every workspace buffer is filled with 0xFF (NaN / -1) before a solve — a read of memory the
+                   // solve did not write shows up as a changed result (tests: results must not depend on it)
   struct GuardedAlloc { void* user; void* base; size_t bytes; };
   std::vector<GuardedAlloc> guarded;
   int spec_w = 0;                                      // MPCB_SPECW env: fixed speculation window (0 = device policy)
@@ -412,6 +414,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
     if (g == 1 || g == 8) h->tile_override = g;
   }
   if (const char* e = std::getenv("MPCB_GUARDS")) h->guards = std::atoi(e) != 0;
+  if (const char* e = std::getenv("MPCB_POISON")) h->poison = std::atoi(e) != 0;
   if (const char* e = std::getenv("MPCB_EXACT")) { if (std::atoi(e) != 0) h->kd.exact = 1; }
   if (const char* e = std::getenv("MPCB_SPECW")) { int w = std::atoi(e); if (w >= 1 && w <= 7) h->spec_w = w; }
   if (const char* e = std::getenv("MPCB_SPEC_LIVE")) {
@@ -632,6 +635,10 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
   if ((rc = grow(h, &h->ws, &h->ws_cap, (size_t)LM.total * ns * sizeof(double), st))) return rc;
   if ((rc = grow(h, &h->wst, &h->wst_cap, (size_t)TM.total * nt * sizeof(double), st))) return rc;
   CK(cudaMemsetAsync(h->queue, 0, sizeof(unsigned long long), st));
+  if (h->poison) {
+    CK(cudaMemsetAsync(h->ws, 0xFF, (size_t)LM.total * ns * sizeof(double), st));
+    CK(cudaMemsetAsync(h->wst, 0xFF, (size_t)TM.total * nt * sizeof(double), st));
+  }
   if ((rc = grow(h, &h->gam, &h->gam_cap, (size_t)B * sizeof(double), st))) return rc;
   h->gam_B = B;
   if ((rc = grow(h, &h->ifail, &h->ifail_cap, (size_t)B * sizeof(int32_t), st))) return rc;
@@ -676,6 +683,11 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
       CK(cudaMallocHost((void**)&h->rs_counters_host, 64 * 4 * sizeof(unsigned)));
     }
     CK(cudaMemsetAsync(h->rs_counters, 0, 16 * sizeof(unsigned), st));
+    if (h->poison) {
+      CK(cudaMemsetAsync(h->rs_d, 0xFF, (size_t)MPCB_SD_ROWS * ns * sizeof(double), st));
+      CK(cudaMemsetAsync(h->rs_i, 0xFF, (size_t)MPCB_SI_ROWS * ns * sizeof(int32_t), st));
+      CK(cudaMemsetAsync(h->rs_escr, 0xFF, (size_t)k.N * stage_doubles * ens * sizeof(double), st));
+    }
     const size_t key_ints = (size_t)2 * MPCB_NKEY * (1 + (size_t)nt);
     if ((rc = grow(h, &h->rs_keys, &h->rs_keys_cap, key_ints * sizeof(int32_t), st))) return rc;
     CK(cudaMemsetAsync(h->rs_keys, 0, (size_t)2 * MPCB_NKEY * sizeof(int32_t), st));
@@ -692,7 +704,9 @@ int mpcb_solve(MpcHandle* h, const MpcSolverParams* sp, int64_t B, const double*
     EvalArgs e;
     std::memset(&e, 0, sizeof(e));
     e.ns = ns; e.nt = nt; e.ens = ens; e.G = G;
-    e.x0 = x0; e.p = p; e.obs = obs; e.lam = lambda; e.sig_base = h->wst + (size_t)TM.SIG * nt; e.ra = ra;
+    e.x0 = x0; e.p = p; e.obs = obs; e.lam = lambda; e.ra = ra;
+    e.tp_base = h->wst + (size_t)TM.vec_total * nt; e.tp_rows = TM.total - TM.vec_total; e.sig_row = TM.SIG - TM.vec_total;
+    e.erows = k.N * stage_doubles;
     e.req_want = a.req_want; e.req_b = a.req_b; e.req_p = a.req_p; e.req_g = a.req_g; e.req_val = a.req_val;
     e.list_grad = a.list_grad; e.list_val = a.list_val; e.escr = h->rs_escr; e.ctl = h->rs_counters + 8;
     e.split_ok = h->split_ok; e.pit_ok = h->pit_ok; e.work_blocks = (int)wblocks;

@@ -238,10 +238,10 @@ MPCB_DEV void road_geom(const RoadView& r, int idx, RoadGeom& g) {
 MPCB_DEV void road_errors(const RoadGeom& g, double px, double py, double phi, double* cte, double* he,
                           double* pe) {
   double vx = px - g.ax, vy = py - g.ay;
-  *cte = vx * g.wy - vy * g.wx;
+  *cte = fma(vx, g.wy, -(vy * g.wx));
   *he = wrap_to_pi(g.hd - phi);
   double v2x = px - g.nx, v2y = py - g.ny;
-  *pe = v2x * g.w2y - v2y * g.w2x;
+  *pe = fma(v2x, g.w2y, -(v2y * g.w2x));
 }
 
 // dpf_test.py:81-102, one obstacle; g4 (nullable) accumulates d/d(x, y, phi, v).
@@ -331,14 +331,14 @@ MPCB_DEV double stage_cost(const KDesc& d, const RoadView& r, const Extras& ex, 
   road_errors(g, y[0], y[1], y[2], &cte, &he, &pe);
   double speed;
   if constexpr (MODEL == MPCB_MODEL_KINEMATIC4) speed = y[3];
-  else speed = sqrt(y[3] * y[3] + y[4] * y[4]);
+  else speed = sqrt(fma(y[3], y[3], y[4] * y[4]));
   double dv = speed - d.v_ref;
-  double L = d.c[0] * dv * dv + d.c[1] * cte * cte + d.c[2] * pe * pe + d.c[3] * he * he + d.c[4] * udl * udl +
-             d.c[5] * ud * ud;
+  // (explicit fma() chain: the build uses -fmad=false)
+  double L = fma(d.c[5] * ud, ud, fma(d.c[4] * udl, udl, fma(d.c[3] * he, he, fma(d.c[2] * pe, pe, fma(d.c[1] * cte, cte, d.c[0] * dv * dv)))));
   if (GRAD) {
     double a1 = 2.0 * d.c[1] * cte, a2 = 2.0 * d.c[2] * pe;
-    gy[0] = a1 * g.wy + a2 * g.w2y;
-    gy[1] = -a1 * g.wx - a2 * g.w2x;
+    gy[0] = fma(a1, g.wy, a2 * g.w2y);
+    gy[1] = -fma(a1, g.wx, a2 * g.w2x);
     gy[2] = -2.0 * d.c[3] * he;
     if constexpr (MODEL == MPCB_MODEL_KINEMATIC4) {
       gy[3] = 2.0 * d.c[0] * dv;

@@ -53,6 +53,7 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     kq[3] = fma(ffy * v.lf, su.cdl, -(fry * v.lr)) * v.inv_iz;
     if (GRAD) {
       L.s = s; L.c = c; L.f0 = kp[0]; L.f1 = kp[1];
+      // (explicit fma() throughout: the build uses -fmad=false, see __graft_entry__.py)
       const double Gf = v.df * ctf * v.cf * v.bf * fm_rcp(fma(zf, zf, 1.0));
       const double Gr = v.dr * ctr * v.cr * v.br * fm_rcp(fma(zr, zr, 1.0));
       const double vx2 = vx * vx;
@@ -66,18 +67,18 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
       const double Pr1 = Gr * a_r * idr, Pr2 = Gr * vx * idr;
       const double sm = su.sdl * v.inv_m, cm = su.cdl * v.inv_m, lc = v.lf * su.cdl * v.inv_iz, lri = v.lr * v.inv_iz;
       // d ffy = Pf1 dvx - Pf2 dvy - Pf2 lf dw + Gf ddelta ;  d fry = -Pr1 dvx - Pr2 dvy + Pr2 lr dw
-      L.a11 = (-v.cm2 * su.d - 2.0 * v.cr2 * vx) * v.inv_m - sm * Pf1;
-      L.a12 = sm * Pf2 + w;
-      L.a13 = sm * Pf2 * v.lf + vy;
-      L.a21 = -Pr1 * v.inv_m + cm * Pf1 - w;
-      L.a22 = -Pr2 * v.inv_m - cm * Pf2;
-      L.a23 = Pr2 * v.lr * v.inv_m - cm * Pf2 * v.lf - vx;
-      L.a31 = lc * Pf1 + lri * Pr1;
-      L.a32 = -lc * Pf2 + lri * Pr2;
-      L.a33 = -lc * Pf2 * v.lf - lri * Pr2 * v.lr;
-      L.bd = (v.cm1 - v.cm2 * vx) * v.inv_m;
-      const double gl = Gf * su.cdl - ffy * su.sdl;
-      L.bl1 = -(Gf * su.sdl + ffy * su.cdl) * v.inv_m;
+      L.a11 = fma(-sm, Pf1, fma(-(2.0 * v.cr2), vx, -(v.cm2 * su.d)) * v.inv_m);
+      L.a12 = fma(sm, Pf2, w);
+      L.a13 = fma(sm * Pf2, v.lf, vy);
+      L.a21 = fma(cm, Pf1, -(Pr1 * v.inv_m)) - w;
+      L.a22 = fma(-cm, Pf2, -(Pr2 * v.inv_m));
+      L.a23 = fma(-(cm * Pf2), v.lf, (Pr2 * v.lr) * v.inv_m) - vx;
+      L.a31 = fma(lc, Pf1, lri * Pr1);
+      L.a32 = fma(-lc, Pf2, lri * Pr2);
+      L.a33 = fma(-(lc * Pf2), v.lf, -((lri * Pr2) * v.lr));
+      L.bd = fma(-v.cm2, vx, v.cm1) * v.inv_m;
+      const double gl = fma(Gf, su.cdl, -(ffy * su.sdl));
+      L.bl1 = -fma(Gf, su.sdl, ffy * su.cdl) * v.inv_m;
       L.bl2 = gl * v.inv_m;
       L.bl3 = gl * v.lf * v.inv_iz;
     }
@@ -489,7 +490,7 @@ __device__ __noinline__ double eval_fm(RoadView r, Extras ex, const double* x0, 
       const double ud = U(2 * n), udl = U(2 * n + 1);
       grad.set(2 * n, fma(2.0 * d.c[5], ud, dots[ND - 2]));
       grad.set(2 * n + 1, fma(2.0 * d.c[4], udl, dots[ND - 1]));
-      lam[2] = lam[2] - dy * lam[0] + dx * lam[1];
+      lam[2] = fma(dx, lam[1], fma(-dy, lam[0], lam[2]));
 #pragma unroll
       for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
     }
@@ -637,7 +638,7 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
     const double ud = U(2 * n), udl = U(2 * n + 1);
     grad.set(2 * n, fma(2.0 * d.c[5], ud, dots[ND - 2]));
     grad.set(2 * n + 1, fma(2.0 * d.c[4], udl, dots[ND - 1]));
-    lam[2] = lam[2] - dy * lam[0] + dx * lam[1];
+    lam[2] = fma(dx, lam[1], fma(-dy, lam[0], lam[2]));
 #pragma unroll
     for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
   }
@@ -800,7 +801,7 @@ __device__ __noinline__ double eval_fm_pit(RoadView r, Extras ex, const double* 
         const double ud = UU[2 * n], udl = UU[2 * n + 1];
         grad.set(2 * n, fma(2.0 * d.c[5], ud, dots[ND - 2]));
         grad.set(2 * n + 1, fma(2.0 * d.c[4], udl, dots[ND - 1]));
-        lam[2] = lam[2] - dy * lam[0] + dx * lam[1];
+        lam[2] = fma(dx, lam[1], fma(-dy, lam[0], lam[2]));
 #pragma unroll
         for (int j = 0; j < ND - 2; ++j) lam[3 + j] = dots[j];
       }

@@ -24,8 +24,12 @@
 // diverges even though tiles are at different PANOC iterations.  Finished tiles pull the next
 // instance from a global queue.
 //
-// Workspace.  Per-lane rows (iterate banks, candidate, stage Jacobians) are lane-interleaved: a
-// warp's access to element i of 32 lanes is one 256-byte transaction.  Per-tile vectors (q, L-BFGS
+// Workspace.  Per-lane rows (iterate banks, candidate, stage Jacobians) are lane-interleaved in BLOCKS of 32 lanes
+// ([block][row][lane in block], MPCB_LB): a warp's access to element i of its 32 lanes is one 256-byte transaction, and the
+// rows of a block are contiguous, so everything a tile touches in a round lies within a few dozen KB.  (Round 1 interleaved
+// over ALL lanes, [row][lane]: consecutive elements of a vector were ns * 8 bytes = 4 MB apart at 64K instances, every
+// access of a tile's serial chains landed on another 2 MB page, and a transition launch for a handful of tiles cost
+// 95 us against 32 us for the same work at B = 1.)  Per-tile vectors (q, L-BFGS
 // history) use a tile-vector layout in which the G lanes of a tile own G consecutive doubles, so the
 // two-loop recursion is split over the lanes with coalesced accesses and tile-shuffle dot products.
 // Locations shared by a tile are either written by their owner lane, or written by every lane with
@@ -49,19 +53,19 @@ struct SolveArgs {
   double* trace;       // optional [B, trace_cap, 4]: (psi, phi_gamma, gamma, accepted candidate) at the top of every inner iteration (the progress callback's info)
   int trace_cap;
   double* gam_out;  // [B] final step size gamma of every instance's last PANOC run (alpaqa's inner stats: final γ)
-  double* ws;    // per-lane rows   [LaneMap.total, ns]
-  double* wst;   // per-tile data   [TileMap.total, nt] (tile-vector region first, plain rows after)
+  double* ws;    // per-lane rows   [ns / MPCB_LB][LaneMap.total][MPCB_LB]
+  double* wst;   // per-tile data: tile vectors [ns / MPCB_LB][vec rows][MPCB_LB], then plain rows [ns / MPCB_LB][rows][MPCB_LB / G]
   int64_t ns, nt;
   unsigned long long* queue;
   long long* dbg;  // optional [warps, 4]: cycles in evaluation / transition phases, rounds, gradient rounds
   // ---- round mode (k_solve<.., ROUND = true> + k_eval_requests, see below) ----
   int round;                 // index of this transition launch (host-driven loop)
   const unsigned* round_ptr; // graph-driven loop: the round index lives in device memory (ctl[1]); null otherwise
-  double* sd;                // saved lane state, doubles  [MPCB_SD_ROWS, ns]
-  int32_t* si;               // saved lane state, ints     [MPCB_SI_ROWS, ns]
+  double* sd;                // saved lane state, doubles  [ns / MPCB_LB][MPCB_SD_ROWS][MPCB_LB]
+  int32_t* si;               // saved lane state, ints     [ns / MPCB_LB][MPCB_SI_ROWS][MPCB_LB]
   int32_t* req_want;         // [ns] evaluation request of every lane: 0 none, 1 psi, 2 psi + grad psi, 3 psi + states
   int64_t* req_b;            // [ns] instance
-  double** req_p;            // [ns] point to evaluate (lane-interleaved row, stride ns)
+  double** req_p;            // [ns] point to evaluate (element i at [i * MPCB_LB])
   double** req_g;            // [ns] gradient row (want 2) / state row (want 3)
   double* req_val;           // [ns] psi written by the evaluation kernel
   int32_t* list_grad;        // compacted lanes whose request wants a gradient
@@ -79,11 +83,12 @@ struct SolveArgs {
   const unsigned* ctl;       // [4] device control words: [0] live tiles of the previous round
 };
 constexpr int MPCB_SD_ROWS = 25, MPCB_SI_ROWS = 28;
+constexpr int MPCB_LB = 32;         // lanes per block of the lane-interleaved arrays
 constexpr int MPCB_NKEY = 16;       // transition buckets: one per SolveState, ST_LS_STEP split by phase
 #ifndef MPCB_ROUND_BLOCK_N
 #define MPCB_ROUND_BLOCK_N 128
 #endif
-constexpr int MPCB_ROUND_BLOCK = MPCB_ROUND_BLOCK_N;  // lanes per CTA of a transition launch
+constexpr int MPCB_ROUND_BLOCK = MPCB_ROUND_BLOCK_N;  // lanes per CTA of a transition launch (64 measured 2 % slower: 1 510 vs 1 478 ms per 64K batch)
 
 enum SolveState {
   ST_IDLE = 0, ST_START_PANOC, ST_INIT_G1, ST_LIP_DONE, ST_XHAT_REQ, ST_XHAT_DONE, ST_ITER_TOP, ST_FD_DONE,
@@ -179,7 +184,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   // two-loop recursion scalars (rho_i, alpha_i) of this CTA's tiles: [tile in CTA][2 * mem]
   double* const s_ra = sbox + 2 * n + (threadIdx.x / G) * 2 * mem;
 
-  const int64_t ns = a.ns, nt = a.nt;
+  const int64_t nt = a.nt;
   const int lane = threadIdx.x & 31;
   const int l = lane % G;  // lane within the tile
   const int tbase = lane - l;
@@ -190,13 +195,22 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   const TileMap T(n, G, mem, m, d.bounded != 0);
   const int ne = T.np / G;  // tile-vector elements owned by each lane: e = l + G j
   // row `row` of tile lane `ll` (lane-interleaved)
-  auto WL = [&](int row, int ll) { return Vec{a.ws + (int64_t)row * ns + (slot - l + ll), ns}; };
-  // element i of the tile-vector at offset `off` (off is a multiple of G)
-  double* const wtile = a.wst + tile * G;
-  const int64_t ntG = nt * G;
-  auto tv = [&](int off, int i) -> double& { return wtile[(int64_t)((off + i) / G) * ntG + ((off + i) % G)]; };
-  double* const trow = a.wst + (int64_t)T.vec_total * nt;  // plain per-tile rows
-  auto TR = [&](int off, int i) -> double& { return trow[(int64_t)(off - T.vec_total + i) * nt + tile]; };
+  const int64_t blk = slot / MPCB_LB;              // block of 32 lanes (tiles never straddle blocks: G divides 32)
+  const int lane32 = (int)(slot % MPCB_LB);        // = this thread's lane: the tile groups of a warp map to one block
+  constexpr int TB = MPCB_LB / G;                  // tiles per block
+  double* const wsb = a.ws + blk * ((int64_t)M.total * MPCB_LB) + (lane32 - l);
+  auto WL = [&](int row, int ll) { return Vec{wsb + (int64_t)row * MPCB_LB + ll, MPCB_LB}; };
+  // element i of the tile-vector at offset `off` (off is a multiple of G): [block][(off + i) / G][tile in block][(off + i) % G]
+  const int VR = T.vec_total / G;                  // rows of G elements in the tile-vector region
+  double* const wtv = a.wst + blk * ((int64_t)VR * MPCB_LB) + (lane32 - l);
+  auto tv = [&](int off, int i) -> double& { return wtv[(int64_t)((off + i) / G) * MPCB_LB + ((off + i) % G)]; };
+  // plain per-tile rows behind the tile-vector region: [block][row][tile in block]
+  const int PR = T.total - T.vec_total;
+  double* const wtp = a.wst + (int64_t)T.vec_total * nt + blk * ((int64_t)PR * TB) + (lane32 - l) / G;
+  auto TR = [&](int off, int i) -> double& { return wtp[(int64_t)(off - T.vec_total + i) * TB]; };
+  // saved lane state (round mode): [block][row][lane in block]
+  int32_t* const sib = ROUND ? a.si + blk * ((int64_t)MPCB_SI_ROWS * MPCB_LB) + lane32 : nullptr;
+  double* const sdb = ROUND ? a.sd + blk * ((int64_t)MPCB_SD_ROWS * MPCB_LB) + lane32 : nullptr;
   auto tsync = [&]() { __syncwarp(tmask); };
   auto tsum = [&](double x) {
 #pragma unroll
@@ -255,23 +269,23 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
   bool dead = notile;  // round mode: this group has no tile / its tile has no instance left
   if constexpr (ROUND) {
     if (rnd > 0 && !notile) {
-      const int fl = a.si[slot];
+      const int fl = sib[0];
       exhausted = fl & 1; fd_ready = fl & 2; c_valid = fl & 4; c_pend = fl & 8; c_rq = fl & 16; c_fb = fl & 32;
       c_acc = fl & 64; c_started = fl & 128; fd_done = fl & 256; c_needg = fl & 512;
       dead = fl & 1024;
       if (!dead) {
         int r = 1;
-#define X(v) v = a.si[(int64_t)(r++) * ns + slot];
+#define X(v) v = sib[(r++) * MPCB_LB];
         MPCB_STATE_I(X)
 #undef X
-        specmask = (unsigned)a.si[(int64_t)(r++) * ns + slot];
+        specmask = (unsigned)sib[(r++) * MPCB_LB];
         r = 0;
-#define X(v) v = a.sd[(int64_t)(r++) * ns + slot];
+#define X(v) v = sdb[(r++) * MPCB_LB];
         MPCB_STATE_D(X)
 #undef X
-        mask0 = (unsigned long long)__double_as_longlong(a.sd[(int64_t)(r++) * ns + slot]);
-        mask1 = (unsigned long long)__double_as_longlong(a.sd[(int64_t)(r++) * ns + slot]);
-        b = __double_as_longlong(a.sd[(int64_t)(r++) * ns + slot]);
+        mask0 = (unsigned long long)__double_as_longlong(sdb[(r++) * MPCB_LB]);
+        mask1 = (unsigned long long)__double_as_longlong(sdb[(r++) * MPCB_LB]);
+        b = __double_as_longlong(sdb[(r++) * MPCB_LB]);
         val = a.req_val[slot];
       }
     }
@@ -301,8 +315,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           double pi = t - xv[k];
           XH.set(i, t);
           P.set(i, pi);
-          s1 += gv[k] * pi;
-          s2 += pi * pi;
+          s1 = fma(gv[k], pi, s1);
+          s2 = fma(pi, pi, s2);
         }
       }
     }
@@ -352,7 +366,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         double sy = 0.0, yy = 0.0, sq = 0.0;
 #pragma unroll
         for (int j = 0; j < NQ; ++j)
-          if (own[j]) { sy += sv[j] * yv[j]; yy += yv[j] * yv[j]; sq += sv[j] * q[j]; }
+          if (own[j]) { sy = fma(sv[j], yv[j], sy); yy = fma(yv[j], yv[j], yy); sq = fma(sv[j], q[j], sq); }
         sy = tsum(sy); yy = tsum(yy); sq = tsum(sq);
         if (!(sy > 0.0)) { s_ra[i] = nan(""); continue; }
         double rho = 1.0 / sy;
@@ -362,7 +376,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         s_ra[mem + i] = al;
 #pragma unroll
         for (int j = 0; j < NQ; ++j)
-          if (own[j]) q[j] -= al * yv[j];
+          if (own[j]) q[j] = fma(-al, yv[j], q[j]);
       }
       if (!(H0 >= 0.0)) H0 = gam;
 #pragma unroll
@@ -382,12 +396,12 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         double yq = 0.0;
 #pragma unroll
         for (int j = 0; j < NQ; ++j)
-          if (own[j]) yq += yv[j] * q[j];
+          if (own[j]) yq = fma(yv[j], q[j], yq);
         yq = tsum(yq);
         double coef = s_ra[mem + i] - rho * yq;
 #pragma unroll
         for (int j = 0; j < NQ; ++j)
-          if (own[j]) q[j] += coef * sv[j];
+          if (own[j]) q[j] = fma(coef, sv[j], q[j]);
       }
 #pragma unroll
       for (int j = 0; j < NQ; ++j)
@@ -406,7 +420,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           const int e = l + G * (j0 + t);
           if (j0 + t < ne && e < n && mbit(e)) {
             double s = tv(T.LS + i * T.np, e), y = tv(T.LY + i * T.np, e);
-            syc[t] += s * y; yyc[t] += y * y; sqc[t] += s * tv(T.Q, e);
+            syc[t] = fma(s, y, syc[t]); yyc[t] = fma(y, y, yyc[t]); sqc[t] = fma(s, tv(T.Q, e), sqc[t]);
           }
         }
       }
@@ -419,7 +433,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       s_ra[mem + i] = al;
       for (int j = 0; j < ne; ++j) {
         int e = l + G * j;
-        if (e < n && mbit(e)) tv(T.Q, e) -= al * tv(T.LY + i * T.np, e);
+        if (e < n && mbit(e)) tv(T.Q, e) = fma(-al, tv(T.LY + i * T.np, e), tv(T.Q, e));
       }
     }
     if (!(H0 >= 0.0)) H0 = gam;
@@ -439,14 +453,14 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
 #pragma unroll
         for (int t = 0; t < CL; ++t) {
           const int e = l + G * (j0 + t);
-          if (j0 + t < ne && e < n && mbit(e)) yqc[t] += tv(T.LY + i * T.np, e) * tv(T.Q, e);
+          if (j0 + t < ne && e < n && mbit(e)) yqc[t] = fma(tv(T.LY + i * T.np, e), tv(T.Q, e), yqc[t]);
         }
       }
       const double yq = tsum_c(yqc);
       double coef = s_ra[mem + i] - rho * yq;
       for (int j = 0; j < ne; ++j) {
         int e = l + G * j;
-        if (e < n && mbit(e)) tv(T.Q, e) += coef * tv(T.LS + i * T.np, e);
+        if (e < n && mbit(e)) tv(T.Q, e) = fma(coef, tv(T.LS + i * T.np, e), tv(T.Q, e));
       }
     }
   };
@@ -506,7 +520,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
             qv[k] = in ? tv(T.Q, i0 + k) : 0.0;
           }
 #pragma unroll
-          for (int k = 0; k < 8; ++k) if (i0 + k < n) XN.set(i0 + k, xv[k] + (1.0 - tau) * pv[k] + tau * qv[k]);
+          for (int k = 0; k < 8; ++k) if (i0 + k < n) XN.set(i0 + k, fma(tau, qv[k], fma(1.0 - tau, pv[k], xv[k])));
         }
       }
       evp = XN; evg = WL(M.G(nb), l); want = 2;
@@ -586,7 +600,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           tv(T.XB, i) = xi;
           double h = fmax(fabs(xi) * sp.lip_eps, sp.lip_delta);
           if (l == pl) XE.set(i, xi + h);
-          hh += h * h;
+          hh = fma(h, h, hh);
         }
         k = 0; no_prog = 0; lb_idx = 0; lb_full = 0; fd_ready = false;
         if (G >= 2) {
@@ -608,7 +622,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
         const int pl = G >= 2 ? 1 : 0;
         Vec Gc = WL(M.G(cb), cl), GE = WL(M.G(cb ^ 1), pl);
         double dd = 0.0;
-        for (int i = 0; i < n; ++i) { double t = GE(i) - Gc(i); dd += t * t; }
+        for (int i = 0; i < n; ++i) { double t = GE(i) - Gc(i); dd = fma(t, t, dd); }
         L = sqrt(dd) / sqrt(hh);
         if (!isfinite(L)) { pstatus = MPCB_STATUS_NOT_FINITE; peps = nan(""); ppsi = psi; state = ST_PANOC_EXIT; continue; }
         L = L < sp.L_min ? sp.L_min : (L > sp.L_max ? sp.L_max : L);
@@ -906,8 +920,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
               if (j0 + t < ne && e < n) {
                 double xi = X(e), xni = XN(e);
                 double s = xni - xi, y = GN(e) - Gc(e);
-                syc[t] += s * y;
-                ssc[t] += s * s;
+                syc[t] = fma(s, y, syc[t]);
+                ssc[t] = fma(s, s, ssc[t]);
                 same = same && (xi == xni);
               }
             }
@@ -937,8 +951,8 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           const int cw = __shfl_sync(tmask, c_idx, tbase + jw);
           const double gw = tbcast(gam_n, jw), pw = tbcast(pTp_n, jw);
           if (l == 0)
-            printf("[trace] outer %d k %d rounds %d accepted c=%d lane %d window %d gamma %s fd_ready %d pTp %.3e\n", alm_i, k,
-                   t_rounds, cw, jw, lsw, gw == gam ? "same" : "halved", (int)fd_ready, pw);
+            printf("[trace] outer %d k %d accepted c=%d gamma %.17g pTp %.17g psi %.17g phi %.17g lbfgs %d/%d\n", alm_i, k, cw, gw, pw,
+                   tbcast(psi_n, jw), tbcast(phi_n, jw), lb_idx, lb_full);
         }
         last_c = __shfl_sync(tmask, c_idx, tbase + jw);
         psi = tbcast(psi_n, jw); psi_hat = tbcast(psi_hat_n, jw);
@@ -1089,21 +1103,21 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
           a.key_list[((int64_t)((rnd + 1) & 1) * MPCB_NKEY + key) * nt + s_kbase[key] + rank] = (int32_t)tile;
       }
       if (!was_dead) {  // tiles that were already dead keep their saved flags
-        a.si[slot] = (int)exhausted | (int)fd_ready << 1 | (int)c_valid << 2 | (int)c_pend << 3 | (int)c_rq << 4 | (int)c_fb << 5 |
+        sib[0] = (int)exhausted | (int)fd_ready << 1 | (int)c_valid << 2 | (int)c_pend << 3 | (int)c_rq << 4 | (int)c_fb << 5 |
                      (int)c_acc << 6 | (int)c_started << 7 | (int)fd_done << 8 | (int)c_needg << 9 | (int)dead << 10;
         if (!dead) {
           int r = 1;
-#define X(v) a.si[(int64_t)(r++) * ns + slot] = v;
+#define X(v) sib[(r++) * MPCB_LB] = v;
           MPCB_STATE_I(X)
 #undef X
-          a.si[(int64_t)(r++) * ns + slot] = (int)specmask;
+          sib[(r++) * MPCB_LB] = (int)specmask;
           r = 0;
-#define X(v) a.sd[(int64_t)(r++) * ns + slot] = v;
+#define X(v) sdb[(r++) * MPCB_LB] = v;
           MPCB_STATE_D(X)
 #undef X
-          a.sd[(int64_t)(r++) * ns + slot] = __longlong_as_double((long long)mask0);
-          a.sd[(int64_t)(r++) * ns + slot] = __longlong_as_double((long long)mask1);
-          a.sd[(int64_t)(r++) * ns + slot] = __longlong_as_double((long long)b);
+          sdb[(r++) * MPCB_LB] = __longlong_as_double((long long)mask0);
+          sdb[(r++) * MPCB_LB] = __longlong_as_double((long long)mask1);
+          sdb[(r++) * MPCB_LB] = __longlong_as_double((long long)b);
         }
       }
       return;
@@ -1116,7 +1130,7 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
     if (want) {
       RoadView r = road_view(a.ra, sroad, d.S, b);
       Extras ex{a.obs ? a.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? a.lam + b * m : nullptr,
-                d.bounded ? &TR(T.SIG, 0) : nullptr, 1, nt};
+                d.bounded ? &TR(T.SIG, 0) : nullptr, 1, TB};
       double y0[NX];
 #pragma unroll
       for (int i = 0; i < NX; ++i) y0[i] = a.x0[b * NX + i];
@@ -1150,7 +1164,9 @@ struct EvalArgs {
   int64_t ns, nt, ens;
   int G;
   const double *x0, *p, *obs, *lam;
-  const double* sig_base;   // ALM penalties: sig_base[r * nt + tile]
+  const double* tp_base;    // plain per-tile rows [block][row][tile in block]; ALM penalties = rows sig_row ..
+  int tp_rows, sig_row;     // rows per tile of that region, first penalty row
+  int erows;                // rows of the evaluation scratch per lane (N * stage doubles), blocked like the workspace
   RoadArg ra;
   const int32_t* req_want;
   const int64_t* req_b;
@@ -1194,7 +1210,13 @@ k_eval_requests(KDesc d, EvalArgs e) {
   stage_problem(d, e.p);
   const int lane = threadIdx.x & 31;
   const int64_t eslot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const Vec scr{e.escr + eslot, e.ens};
+  const Vec scr{e.escr + (eslot / MPCB_LB) * ((int64_t)e.erows * MPCB_LB) + (eslot % MPCB_LB), MPCB_LB};
+  // ALM penalties of the tile that owns lane `slot`: first row and stride between rows
+  auto sig_of = [&](int64_t slot) -> const double* {
+    const int TBe = MPCB_LB / e.G;
+    return e.tp_base + (slot / MPCB_LB) * ((int64_t)e.tp_rows * TBe) + (int64_t)e.sig_row * TBe + (slot % MPCB_LB) / e.G;
+  };
+  const int64_t sig_stride = MPCB_LB / e.G;
   if (e.round_ptr) {  // graph-driven loop: this round's buffers
     const unsigned r = *e.round_ptr;
     e.counters = e.counters_base + 4 * (r & 1u);
@@ -1220,12 +1242,11 @@ k_eval_requests(KDesc d, EvalArgs e) {
     if (ridx < ng) {
       const int64_t slot = e.list_grad[ridx];
       const int64_t b = e.req_b[slot];
-      const int64_t tile = slot / e.G;
       RoadView r = road_view(e.ra, sroad, d.S, b);
       Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
-                d.bounded ? e.sig_base + tile : nullptr, 1, e.nt};
+                d.bounded ? sig_of(slot) : nullptr, 1, sig_stride};
       double v = 0.0;
-      if constexpr (Fm<MODEL>::PIT) v = eval_fm_pit<MODEL>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], e.ns}, Vec{e.req_g[slot], e.ns}, pit_sm, !d.exact);
+      if constexpr (Fm<MODEL>::PIT) v = eval_fm_pit<MODEL>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], MPCB_LB}, Vec{e.req_g[slot], MPCB_LB}, pit_sm, !d.exact);
       if (threadIdx.x == 0) e.req_val[slot] = v;
       return;  // (a CTA with a parallel-in-time request takes no chunks: nb below keeps them apart)
     }
@@ -1261,15 +1282,14 @@ k_eval_requests(KDesc d, EvalArgs e) {
       if (ridx < ng) {
         const int64_t slot = e.list_grad[ridx];
         const int64_t b = e.req_b[slot];
-        const int64_t tile = slot / e.G;
         RoadView r = road_view(e.ra, sroad, d.S, b);
         Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
-                  d.bounded ? e.sig_base + tile : nullptr, 1, e.nt};
+                  d.bounded ? sig_of(slot) : nullptr, 1, sig_stride};
         double y0[NX];
 #pragma unroll
         for (int i = 0; i < NX; ++i) y0[i] = e.x0[b * NX + i];
-        const Vec scr_lead{e.escr + (eslot - J), e.ens};
-        const double v = eval_fm_split<MODEL>(r, ex, y0, Vec{e.req_p[slot], e.ns}, scr_lead, Vec{e.req_g[slot], e.ns}, J,
+        const Vec scr_lead{scr.p - J, MPCB_LB};
+        const double v = eval_fm_split<MODEL>(r, ex, y0, Vec{e.req_p[slot], MPCB_LB}, scr_lead, Vec{e.req_g[slot], MPCB_LB}, J,
                                               0xffu << (lane & 24));
         if (J == 0) e.req_val[slot] = v;
         nonfinite = J == 0 && !(fabs(v) < 1e300);
@@ -1278,15 +1298,14 @@ k_eval_requests(KDesc d, EvalArgs e) {
       const int64_t slot = grad ? e.list_grad[idx] : e.list_val[idx];
       const int want = e.req_want[slot];
       const int64_t b = e.req_b[slot];
-      const int64_t tile = slot / e.G;
       RoadView r = road_view(e.ra, sroad, d.S, b);
       Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
-                d.bounded ? e.sig_base + tile : nullptr, 1, e.nt};
+                d.bounded ? sig_of(slot) : nullptr, 1, sig_stride};
       double y0[NX];
 #pragma unroll
       for (int i = 0; i < NX; ++i) y0[i] = e.x0[b * NX + i];
-      const Vec pt{e.req_p[slot], e.ns};
-      const Vec out{e.req_g[slot], e.ns};
+      const Vec pt{e.req_p[slot], MPCB_LB};
+      const Vec out{e.req_g[slot], MPCB_LB};
       double v;
       if (grad) v = eval_fm<MODEL, true>(r, ex, y0, pt, scr, out, true, Vec{nullptr, 0}, IVec{nullptr, 0}, !d.exact);
       else v = eval_fm<MODEL, false>(r, ex, y0, pt, scr, Vec{nullptr, 0}, false, want == 3 ? out : Vec{nullptr, 0},

@@ -140,7 +140,7 @@ def best_response_rounds(prob, x0_local, ctrl_local, n_vehicles, rounds=5, U0=No
     the predicted trajectories `[B_local, N, 4]` over the group (NCCL on GPUs) and rebuild each vehicle's obstacle from
     its opponent's row.  Without `cars` the paths are the fixed `ctrl_local` [B_local, 12] (no decision layer).
     Returns dict(U, traj (global [2P, N, 4]), status [rounds, B_local], delta [rounds] = max change of the gathered
-    trajectories between rounds, obs; with `cars`: target [rounds, B_local], payoff, lane_change_frac; with `timing`:
+    trajectories between rounds (delta_median: the median over vehicles of each vehicle's max change), obs; with `cars`: target [rounds, B_local], payoff, lane_change_frac; with `timing`:
     solve_ms / gather_ms per round from CUDA events)."""
     import torch.distributed as dist
     if rank is None:
@@ -168,7 +168,7 @@ def best_response_rounds(prob, x0_local, ctrl_local, n_vehicles, rounds=5, U0=No
         ctrl = None
     else:
         ctrl = prob._t(ctrl_local).reshape(-1, 12)
-    status, delta, prev, targets, payoff = [], [], None, [], None
+    status, delta, delta_med, prev, targets, payoff = [], [], [], None, [], None
     traj_all = None
     ev = []
     for _ in range(rounds):
@@ -194,8 +194,10 @@ def best_response_rounds(prob, x0_local, ctrl_local, n_vehicles, rounds=5, U0=No
             opp_lane = lane_of(traj_all[opp][:, -1, 1], h)
         status.append(st.status)
         delta.append(float("inf") if prev is None else float((traj_all - prev).abs().max().item()))
+        delta_med.append(float("inf") if prev is None else
+                         float((traj_all - prev).abs().flatten(1).max(dim=1).values.median().item()))
         prev = traj_all
-    out = dict(U=U, traj=traj_all, status=torch.stack(status), delta=delta, obs=obs)
+    out = dict(U=U, traj=traj_all, status=torch.stack(status), delta=delta, delta_median=delta_med, obs=obs)
     if game:
         tg = torch.stack(targets)
         out.update(target=tg, payoff=payoff, ctrl=ctrl,
