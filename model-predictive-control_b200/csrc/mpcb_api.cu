@@ -43,7 +43,7 @@ struct MpcHandle {
   int spec_w = 0;                                      // MPCB_SPECW env: fixed speculation window (0 = device policy)
   int spec_live_wide = 4096, spec_live_mid = 12288;    // MPCB_SPEC_LIVE="wide,mid": live-tile thresholds of the policy
   int split_ok = 1;                                    // MPCB_SPLIT env (0: never use the split evaluation)
-  int pit_ok = 1;                                      // MPCB_PIT env (0: never use the parallel-in-time evaluation)
+  int pit_ok = 1;                                      // MPCB_PIT env (0: never use the parallel-in-time evaluation, 2: gradient requests only)
   // Round mode's loop: driven on the device by a CUDA graph (WHILE node; the default: mpcb_solve returns at once), or by
   // the host (MPCB_LOOP=host; also taken when a per-round diagnostic is on: MPCB_ROUND_LOG, MPCB_EVAL_TRACE)
   int loop_graph = 1;
@@ -422,7 +422,7 @@ int mpcb_create(const MpcProblemDesc* desc, MpcHandle** out) {
     if (std::sscanf(e, "%d,%d", &a, &b) == 2 && a >= 0 && b >= a) { h->spec_live_wide = a; h->spec_live_mid = b; }
   }
   if (const char* e = std::getenv("MPCB_SPLIT")) h->split_ok = std::atoi(e) != 0;
-  if (const char* e = std::getenv("MPCB_PIT")) h->pit_ok = std::atoi(e) != 0;
+  if (const char* e = std::getenv("MPCB_PIT")) h->pit_ok = std::atoi(e);
   if (const char* e = std::getenv("MPCB_LOOP")) h->loop_graph = std::strcmp(e, "host") != 0;
   if (const char* e = std::getenv("MPCB_EVAL_TRACE")) h->eval_trace_round = std::atoll(e);
   *out = h;

@@ -715,7 +715,10 @@ __host__ __device__ constexpr int fm_pit_doubles(int N) {
 
 // Called by every thread of the CTA; returns psi on every thread (NaN for a cut request).  `grad` is the request's
 // gradient row (global, strided).
-template <int MODEL>
+// GRAD = false: a psi-only request the same way (phase 2 = the stage costs, phase 3 = their sum in stage order; `grad`
+// is then the optional row of states s_1 .. s_N, as eval_fm<MODEL, false> writes them): 20 stage costs (vertex scan,
+// errors) no longer sit between the model calls of the chain.
+template <int MODEL, bool GRAD>
 __device__ __noinline__ double eval_fm_pit(RoadView r, Extras ex, const double* x0, Vec U, Vec grad, double* sm, bool cut) {
   const KDesc& d = s_desc;
   using M = Fm<MODEL>;
@@ -751,20 +754,26 @@ __device__ __noinline__ double eval_fm_pit(RoadView r, Extras ex, const double* 
   const bool dead = flag[0] != 0.0;
   // ---- phase 2: every stage at once
   if (!dead) {
-    const int J = threadIdx.x & 7;
-    for (int n = threadIdx.x >> 3; n < N; n += blockDim.x >> 3) {
-      const double ud = UU[2 * n], udl = UU[2 * n + 1];
+    if (GRAD) {
+      const int J = threadIdx.x & 7;
       if (J < ND) {
-        double y[NX];
+        for (int n = threadIdx.x >> 3; n < N; n += blockDim.x >> 3) {
+          double y[NX];
 #pragma unroll
-        for (int i = 0; i < NX; ++i) y[i] = S[n * NX + i];
-        stage_fm_split<MODEL>(y, ud, udl, Vec{Jb, 1}, n * K, J);
-      } else if (J == ND) {
-        double y[NX], gy[NX], gu[2];
+          for (int i = 0; i < NX; ++i) y[i] = S[n * NX + i];
+          stage_fm_split<MODEL>(y, UU[2 * n], UU[2 * n + 1], Vec{Jb, 1}, n * K, J);
+        }
+      }
+    }
+    // stage costs: from the LAST lanes of the CTA backwards, so that for the usual horizons they run in warps of their
+    // own beside the tangent warps instead of after them in the same warp
+    for (int n = (int)(blockDim.x - 1u - threadIdx.x); n < N; n += blockDim.x) {
+      double y[NX], gy[NX], gu[2];
 #pragma unroll
-        for (int i = 0; i < NX; ++i) y[i] = S[(n + 1) * NX + i];
-        int idx = -1;
-        Lc[n] = stage_cost<MODEL, true, true>(d, r, ex, n, y, ud, udl, &idx, gy, gu);
+      for (int i = 0; i < NX; ++i) y[i] = S[(n + 1) * NX + i];
+      int idx = -1;
+      Lc[n] = stage_cost<MODEL, GRAD, true>(d, r, ex, n, y, UU[2 * n], UU[2 * n + 1], &idx, gy, gu);
+      if (GRAD) {
 #pragma unroll
         for (int i = 0; i < NX; ++i) Jb[n * K + NX * ND + 2 + i] = gy[i];
       }
@@ -772,7 +781,17 @@ __device__ __noinline__ double eval_fm_pit(RoadView r, Extras ex, const double* 
   }
   __syncthreads();
   // ---- phase 3: cost sum and horizon adjoint
-  if (threadIdx.x == 0) {
+  if (!GRAD) {
+    if (grad.p) {
+      const double nn = nan("");
+      for (int i = threadIdx.x; i < N * NX; i += blockDim.x) grad.set(i, dead ? nn : S[NX + i]);
+    }
+    if (threadIdx.x == 0) {
+      double cost = 0.0;
+      for (int n = 0; n < N; ++n) cost += Lc[n];
+      flag[1] = dead ? nan("") : cost;
+    }
+  } else if (threadIdx.x == 0) {
     if (dead) {
       const double nn = nan("");
       for (int i = 0; i < 2 * N; ++i) grad.set(i, nn);

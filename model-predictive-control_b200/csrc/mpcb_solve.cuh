@@ -1235,22 +1235,30 @@ k_eval_requests(KDesc d, EvalArgs e) {
   const unsigned cv = (nv + 31u) >> 5;
   // Few gradient requests (each can have a CTA of its own next to the psi-only chunks): parallel-in-time evaluation,
   // one request per CTA from the END of the grid (the psi-only chunks are handed out from its start).
-  const bool pit = Fm<MODEL>::PIT && e.pit_ok && ng > 0 && ng + (cv < 8u ? cv : 8u) <= gridDim.x;
+  // Fewer requests than CTAs: the psi-only requests are evaluated that way too, every request on an SM of its own.
+  const bool pit_all = Fm<MODEL>::PIT && e.pit_ok && e.pit_ok != 2 && ng + nv <= gridDim.x;
+  const bool pit = pit_all || (Fm<MODEL>::PIT && e.pit_ok && ng > 0 && ng + (cv < 8u ? cv : 8u) <= gridDim.x);
   if (pit) {
     double* pit_sm = smem + (e.ra.in_smem ? e.ra.R * road_smem_doubles(d.S) : 0);
     const unsigned ridx = gridDim.x - 1u - blockIdx.x;
-    if (ridx < ng) {
-      const int64_t slot = e.list_grad[ridx];
+    if (ridx < ng || (pit_all && ridx < ng + nv)) {
+      const bool grad = ridx < ng;
+      const int64_t slot = grad ? e.list_grad[ridx] : e.list_val[ridx - ng];
       const int64_t b = e.req_b[slot];
       RoadView r = road_view(e.ra, sroad, d.S, b);
       Extras ex{e.obs ? e.obs + b * d.n_obs * MPCB_OBS_DIM : nullptr, d.bounded ? e.lam + b * d.m : nullptr,
                 d.bounded ? sig_of(slot) : nullptr, 1, sig_stride};
       double v = 0.0;
-      if constexpr (Fm<MODEL>::PIT) v = eval_fm_pit<MODEL>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], MPCB_LB}, Vec{e.req_g[slot], MPCB_LB}, pit_sm, !d.exact);
+      if constexpr (Fm<MODEL>::PIT) {
+        if (grad) v = eval_fm_pit<MODEL, true>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], MPCB_LB}, Vec{e.req_g[slot], MPCB_LB}, pit_sm, !d.exact);
+        else v = eval_fm_pit<MODEL, false>(r, ex, e.x0 + b * NX, Vec{e.req_p[slot], MPCB_LB},
+                                           e.req_want[slot] == 3 ? Vec{e.req_g[slot], MPCB_LB} : Vec{nullptr, 0}, pit_sm, !d.exact);
+      }
       if (threadIdx.x == 0) e.req_val[slot] = v;
       return;  // (a CTA with a parallel-in-time request takes no chunks: nb below keeps them apart)
     }
   }
+  if (pit_all) return;
   // CTAs that take chunks: those with evaluation scratch, minus the ones busy with parallel-in-time requests
   unsigned nb = (unsigned)e.work_blocks < gridDim.x ? (unsigned)e.work_blocks : gridDim.x;
   if (pit && gridDim.x - ng < nb) nb = gridDim.x - ng;

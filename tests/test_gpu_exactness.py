@@ -270,12 +270,13 @@ def test_guard_canaries_and_repeat_determinism(mp, mode, monkeypatch):
                                      "kinematic_obstacles_B8_N40"])
 def test_parallel_in_time_evaluation_changes_nothing(mp, problem, monkeypatch):
     """Thin rounds give every gradient request a CTA of its own: the primal rollout by one thread, then all stage
-    Jacobians and stage costs at once from shared memory, then the adjoint (eval_fm_pit).  Same stage arithmetic, same
-    summation orders: bit-identical to the chunked evaluations (MPCB_PIT=0) — for a lone vehicle (every round thin), for
-    batches whose tail is thin, with ALM rows, and for N = 40 (two passes over the stage groups)."""
+    Jacobians and stage costs at once from shared memory, then the adjoint (eval_fm_pit); with fewer requests than SMs
+    the psi-only requests go the same way (MPCB_PIT=2: gradient requests only).  Same stage arithmetic, same summation
+    orders: bit-identical to the chunked evaluations (MPCB_PIT=0) — for a lone vehicle (every round thin), for batches
+    whose tail is thin, with ALM rows (psi + states requests), and for N = 40 (two passes over the stage groups)."""
     monkeypatch.setenv("MPCB_MODE", "rounds")
     out = []
-    for pit in ("0", "1"):
+    for pit in ("0", "2", "1"):
         monkeypatch.setenv("MPCB_PIT", pit)
         if problem == "pacejka_B4_N20":
             _, _, U, _, st = _solve_tracking(mp, 20, 4, seed=8)
@@ -289,7 +290,8 @@ def test_parallel_in_time_evaluation_changes_nothing(mp, problem, monkeypatch):
         else:
             _, _, U, _, st = _solve_lane_change(mp, 40, 8, seed=78)
         out.append((U, st))
-    _assert_same_solution(out[0], out[1], f"{problem}: chunked evaluations vs parallel-in-time")
+    _assert_same_solution(out[0], out[1], f"{problem}: chunked evaluations vs parallel-in-time gradient requests")
+    _assert_same_solution(out[0], out[2], f"{problem}: chunked evaluations vs parallel-in-time for every request")
 
 
 # ------------------------------------------------------------------ 6. the device-driven round loop (CUDA graph WHILE node)
