@@ -205,6 +205,19 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
       }
     }
   }
+  // The model call of a lone thread's primal chain (phase 1 of eval_fm_pit): call_fast's branch-free block is started
+  // at once and the routing test of `call` is evaluated beside it instead of in front of it; an input outside the
+  // fast range is then evaluated again by `call`.  Bits: call<GRAD>'s.
+  template <bool GRAD>
+  static MPCB_DEV void call_primal(const double* q, const StageU& su, const VehP& v, double* kp, double* kq) {
+    const double vx = q[1];
+    const double a_f = fma(q[3], v.lf, q[2]), a_r = fma(q[3], v.lr, -q[2]);
+    const double am = fmax(fabs(a_f), fabs(a_r));
+    const bool fast = vx > 0x1p-960 && vx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX && su.z2_mode == 2 && am <= 0.5 * vx;
+    Lin L;
+    call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
+    if (!fast) call<GRAD>(q, su, v, kp, kq, L);
+  }
   // tangent of one direction J at the same stage point: tq = (phi', vx', vy', w')
   template <int J>
   static MPCB_DEV void tan(const Lin& L, const double* tq, double* tkp, double* tkq) {
@@ -645,11 +658,12 @@ __device__ __noinline__ double eval_fm_split(RoadView r, Extras ex, const double
   return cost;
 }
 
-// Primal-only stage with the GRADIENT variant's arithmetic: the model call is Fm::call<true> (its sincos kernels, not the
-// value-only variant's shorter sin kernel, whose last bits differ), inlined with the linearisation unused, so the
-// compiler drops the Lin computation and every tangent: the state bits are those of stage_fm / stage_fm_split at about
-// the value-only call's latency.  Phase 1 of the parallel-in-time evaluation.
-template <int MODEL>
+// Primal-only stage.  GA: with the GRADIENT variant's arithmetic — the model call is Fm::call<true> (its sincos kernels, not
+// the value-only variant's shorter sin kernel, whose last bits differ), inlined with the linearisation unused, so the
+// compiler drops the Lin computation and every tangent: the state bits are those of stage_fm<MODEL, true> / stage_fm_split
+// at about the value-only call's latency.  !GA: Fm::call<false>, the bits of stage_fm<MODEL, false>.  Phase 1 of the
+// parallel-in-time evaluation of a gradient / a psi-only request.
+template <int MODEL, bool GA>
 MPCB_DEV void rk4_fm_primal(double* p, double* q, const StageU& su, const VehP& v, double h) {
   using M = Fm<MODEL>;
   constexpr int NQ = M::NQ;
@@ -657,15 +671,22 @@ MPCB_DEV void rk4_fm_primal(double* p, double* q, const StageU& su, const VehP& 
   double kp[2] = {0.0, 0.0}, kq[NQ], accp[2] = {0.0, 0.0}, accq[NQ];
 #pragma unroll
   for (int i = 0; i < NQ; ++i) { kq[i] = 0.0; accq[i] = 0.0; }
-#pragma unroll 1
+  // Unrolled, and (Pacejka-6) with the fast block of the model call started before its range test (call_primal): the
+  // end of one call overlaps the start of the next.  Measured on the lone thread of phase 1 (B200, cycles per model
+  // call): rolled + routed 970, rolled + call_primal 880, unrolled + routed 1 040, unrolled + call_primal 700.
+#pragma unroll
   for (int s = 0; s < 4; ++s) {
     const double a = s == 0 ? 0.0 : (s == 3 ? h : 0.5 * h);
     const double bw = (s == 0 || s == 3) ? 1.0 : 2.0;
     double sq[NQ];
 #pragma unroll
     for (int i = 0; i < NQ; ++i) sq[i] = fma(a, kq[i], q[i]);
-    typename M::Lin L;
-    M::template call<true>(sq, su, v, kp, kq, L);
+    if constexpr (MODEL == MPCB_MODEL_PACEJKA6) {
+      M::template call_primal<GA>(sq, su, v, kp, kq);
+    } else {
+      typename M::Lin L;
+      M::template call<GA>(sq, su, v, kp, kq, L);
+    }
     accp[0] = fma(bw, kp[0], accp[0]);
     accp[1] = fma(bw, kp[1], accp[1]);
 #pragma unroll
@@ -677,7 +698,7 @@ MPCB_DEV void rk4_fm_primal(double* p, double* q, const StageU& su, const VehP& 
   for (int i = 0; i < NQ; ++i) q[i] = fma(h6, accq[i], q[i]);
 }
 
-template <int MODEL>
+template <int MODEL, bool GA>
 __device__ __noinline__ void stage_fm_primal(double* pq, double ud, double udl) {
   using M = Fm<MODEL>;
   constexpr int NQ = M::NQ;
@@ -690,7 +711,7 @@ __device__ __noinline__ void stage_fm_primal(double* pq, double ud, double udl) 
   const int n_sub = s_desc.n_sub;
   const double h = s_desc.h;
 #pragma unroll 1
-  for (int e = 0; e < n_sub; ++e) rk4_fm_primal<MODEL>(p, q, su, v, h);
+  for (int e = 0; e < n_sub; ++e) rk4_fm_primal<MODEL, GA>(p, q, su, v, h);
   pq[0] = p[0]; pq[1] = p[1];
 #pragma unroll
   for (int i = 0; i < NQ; ++i) pq[2 + i] = q[i];
@@ -740,7 +761,7 @@ __device__ __noinline__ double eval_fm_pit(RoadView r, Extras ex, const double* 
     for (int i = 0; i < NX; ++i) y[i] = S[i];
 #pragma unroll 1
     for (int n = 0; n < N; ++n) {
-      stage_fm_primal<MODEL>(y, UU[2 * n], UU[2 * n + 1]);
+      stage_fm_primal<MODEL, GRAD>(y, UU[2 * n], UU[2 * n + 1]);
       bool sane = true;
 #pragma unroll
       for (int i = 0; i < NX; ++i) sane = sane && y[i] == y[i];
