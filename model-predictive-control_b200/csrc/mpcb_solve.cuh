@@ -37,6 +37,7 @@
 // between tile barriers.
 #pragma once
 #include <float.h>
+#include <type_traits>
 #include "mpcb_fwd.cuh"
 
 namespace mpcb {
@@ -346,66 +347,77 @@ k_solve(KDesc d, MpcSolverParams sp, SolveArgs a) {
       }
     }
     if (ROUND && ne <= NQ) {  // (the persistent kernel has no registers to spare: it spilled with this path)
-      double q[NQ];
-      bool own[NQ];
+      // The rows of a pair are loaded UNCONDITIONALLY, all at once (padding lanes read the row's padding, elements outside
+      // the inactive set are read and not used): written as `own ? load : 0` every load sat behind its own branch next
+      // to its use and the ten of them took ten L2 round trips, 2 000 cycles per pair and loop on a lone tile (B200,
+      // clock64 around the statements) — 46 us of an 80 us transition launch at 20 pairs.
+      auto run = [&](auto nqc) {
+        constexpr int NQc = decltype(nqc)::value;
+        double q[NQc];
+        bool own[NQc];
 #pragma unroll
-      for (int j = 0; j < NQ; ++j) {
-        const int e = l + G * j;
-        own[j] = j < ne && e < n && mbit(e);
-        q[j] = own[j] ? tv(T.Q, e) : 0.0;
-      }
-      for (int kk = 0; kk < cnt; ++kk) {
-        int i = lb_idx - 1 - kk;
-        if (i < 0) i += mem;
-        double sv[NQ], yv[NQ];
-#pragma unroll
-        for (int j = 0; j < NQ; ++j) {
-          sv[j] = own[j] ? tv(T.LS + i * T.np, l + G * j) : 0.0;
-          yv[j] = own[j] ? tv(T.LY + i * T.np, l + G * j) : 0.0;
+        for (int j = 0; j < NQc; ++j) {
+          const int e = l + G * j;
+          own[j] = j < ne && e < n && mbit(e);
+          q[j] = tv(T.Q, l + G * (j < ne ? j : ne - 1));
         }
-        double sy = 0.0, yy = 0.0, sq = 0.0;
 #pragma unroll
-        for (int j = 0; j < NQ; ++j)
-          if (own[j]) { sy = fma(sv[j], yv[j], sy); yy = fma(yv[j], yv[j], yy); sq = fma(sv[j], q[j], sq); }
-        sy = tsum(sy); yy = tsum(yy); sq = tsum(sq);
-        if (!(sy > 0.0)) { s_ra[i] = nan(""); continue; }
-        double rho = 1.0 / sy;
-        s_ra[i] = rho;
-        if (H0 < 0.0) H0 = sy / yy;
-        double al = rho * sq;
-        s_ra[mem + i] = al;
+        for (int j = 0; j < NQc; ++j) q[j] = own[j] ? q[j] : 0.0;
+        auto load_pair = [&](int i, double* sv, double* yv) {
 #pragma unroll
-        for (int j = 0; j < NQ; ++j)
-          if (own[j]) q[j] = fma(-al, yv[j], q[j]);
-      }
-      if (!(H0 >= 0.0)) H0 = gam;
+          for (int j = 0; j < NQc; ++j) {
+            const int e = l + G * (j < ne ? j : ne - 1);
+            sv[j] = tv(T.LS + i * T.np, e);
+            yv[j] = tv(T.LY + i * T.np, e);
+          }
+        };
+        for (int kk = 0; kk < cnt; ++kk) {
+          int i = lb_idx - 1 - kk;
+          if (i < 0) i += mem;
+          double sv[NQc], yv[NQc];
+          load_pair(i, sv, yv);
+          double sy = 0.0, yy = 0.0, sq = 0.0;
 #pragma unroll
-      for (int j = 0; j < NQ; ++j)
-        if (own[j]) q[j] *= H0;
-      for (int kk = cnt - 1; kk >= 0; --kk) {
-        int i = lb_idx - 1 - kk;
-        if (i < 0) i += mem;
-        double rho = s_ra[i];
-        if (isnan(rho)) continue;
-        double sv[NQ], yv[NQ];
+          for (int j = 0; j < NQc; ++j)
+            if (own[j]) { sy = fma(sv[j], yv[j], sy); yy = fma(yv[j], yv[j], yy); sq = fma(sv[j], q[j], sq); }
+          sy = tsum(sy); yy = tsum(yy); sq = tsum(sq);
+          if (!(sy > 0.0)) { s_ra[i] = nan(""); continue; }
+          double rho = 1.0 / sy;
+          s_ra[i] = rho;
+          if (H0 < 0.0) H0 = sy / yy;
+          double al = rho * sq;
+          s_ra[mem + i] = al;
 #pragma unroll
-        for (int j = 0; j < NQ; ++j) {
-          sv[j] = own[j] ? tv(T.LS + i * T.np, l + G * j) : 0.0;
-          yv[j] = own[j] ? tv(T.LY + i * T.np, l + G * j) : 0.0;
+          for (int j = 0; j < NQc; ++j)
+            if (own[j]) q[j] = fma(-al, yv[j], q[j]);
         }
-        double yq = 0.0;
+        if (!(H0 >= 0.0)) H0 = gam;
 #pragma unroll
-        for (int j = 0; j < NQ; ++j)
-          if (own[j]) yq = fma(yv[j], q[j], yq);
-        yq = tsum(yq);
-        double coef = s_ra[mem + i] - rho * yq;
+        for (int j = 0; j < NQc; ++j)
+          if (own[j]) q[j] *= H0;
+        for (int kk = cnt - 1; kk >= 0; --kk) {
+          int i = lb_idx - 1 - kk;
+          if (i < 0) i += mem;
+          double rho = s_ra[i];
+          if (isnan(rho)) continue;
+          double sv[NQc], yv[NQc];
+          load_pair(i, sv, yv);
+          double yq = 0.0;
 #pragma unroll
-        for (int j = 0; j < NQ; ++j)
-          if (own[j]) q[j] = fma(coef, sv[j], q[j]);
-      }
+          for (int j = 0; j < NQc; ++j)
+            if (own[j]) yq = fma(yv[j], q[j], yq);
+          yq = tsum(yq);
+          double coef = s_ra[mem + i] - rho * yq;
 #pragma unroll
-      for (int j = 0; j < NQ; ++j)
-        if (own[j]) tv(T.Q, l + G * j) = q[j];
+          for (int j = 0; j < NQc; ++j)
+            if (own[j]) q[j] = fma(coef, sv[j], q[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < NQc; ++j)
+          if (own[j]) tv(T.Q, l + G * j) = q[j];
+      };
+      if (ne <= 5) run(std::integral_constant<int, 5>{});
+      else run(std::integral_constant<int, NQ>{});
       return;
     }
     for (int kk = 0; kk < cnt; ++kk) {
