@@ -267,7 +267,7 @@ def test_guard_canaries_and_repeat_determinism(mp, mode, monkeypatch):
 
 # ------------------------------------------------------------------ 5. the parallel-in-time evaluation of thin rounds
 @pytest.mark.parametrize("problem", ["pacejka_B4_N20", "pacejka_B40_N20", "pacejka_B2048_N12", "pacejka_bounded_B6_N12",
-                                     "kinematic_obstacles_B8_N40"])
+                                     "pacejka_B12_N40", "kinematic_obstacles_B8_N40"])
 def test_parallel_in_time_evaluation_changes_nothing(mp, problem, monkeypatch):
     """Thin rounds give every gradient request a CTA of its own: the primal rollout by one thread, then all stage
     Jacobians and stage costs at once from shared memory, then the adjoint (eval_fm_pit); with fewer requests than SMs
@@ -284,6 +284,8 @@ def test_parallel_in_time_evaluation_changes_nothing(mp, problem, monkeypatch):
             _, _, U, _, st = _solve_tracking(mp, 20, 40, seed=9)
         elif problem == "pacejka_B2048_N12":
             _, _, U, _, st = _solve_tracking(mp, 12, 2048, seed=10)
+        elif problem == "pacejka_B12_N40":
+            _, _, U, _, st = _solve_tracking(mp, 40, 12, seed=12)
         elif problem == "pacejka_bounded_B6_N12":
             _, _, U, _, st = _solve_tracking(mp, 12, 6, seed=31, flags=mp.FLAG_BOUNDED_D, lam=True, D_lower=[-np.inf] * 6,
                                              D_upper=[np.inf, np.inf, np.inf, -1.0, np.inf, np.inf])
