@@ -31,7 +31,7 @@ def main():
             os.environ.pop("MPCB_TILE", None)
         prob = mpcb200.BatchedMpc(N=N, S=100, road_mode=mpcb200.ROAD_TABLE, n_roads=2)
         dev = prob.device
-        w = wl.tracking_batch(B, N, 100, seed=2)
+        w = wl.tracking_batch(B, N, 100, seed=int(os.environ.get("PROBE_SEED", "2")))
         x0, road = torch.tensor(w["x0"], device=dev), torch.tensor(w["road"], device=dev)
         ridx, U0 = torch.tensor(w["road_idx"], device=dev), torch.tensor(w["U0"], device=dev)
         best, st = 1e30, None
