@@ -218,6 +218,16 @@ template <> struct Fm<MPCB_MODEL_PACEJKA6> {
     call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
     if (!fast) call<GRAD>(q, su, v, kp, kq, L);
   }
+  // The same with the linearisation kept (the split evaluation's lanes: few warps per SM there too).
+  template <bool GRAD>
+  static MPCB_DEV void call_spec(const double* q, const StageU& su, const VehP& v, double* kp, double* kq, Lin& L) {
+    const double vx = q[1];
+    const double a_f = fma(q[3], v.lf, q[2]), a_r = fma(q[3], v.lr, -q[2]);
+    const double am = fmax(fabs(a_f), fabs(a_r));
+    const bool fast = vx > 0x1p-960 && vx < 0x1p960 && fabs(q[0]) < MPCB_FM_TRIG_MAX && su.z2_mode == 2 && am <= 0.5 * vx;
+    call_fast<GRAD, true>(q, su, v, a_f, a_r, kp, kq, L);
+    if (!fast) call<GRAD>(q, su, v, kp, kq, L);
+  }
   // tangent of one direction J at the same stage point: tq = (phi', vx', vy', w')
   template <int J>
   static MPCB_DEV void tan(const Lin& L, const double* tq, double* tkp, double* tkq) {
@@ -535,7 +545,11 @@ MPCB_DEV void rk4_fm_split(double* p, double* q, double* tp, double* tq, int J, 
 #pragma unroll
     for (int i = 0; i < NQ; ++i) sq[i] = fma(a, kq[i], q[i]);
     typename M::Lin L;
-    M::template call<true>(sq, su, v, kp, kq, L);
+    // (Pacejka-6: fast block before its range test, as in the lone thread's primal chain — the split lanes run with one or
+    // two warps per SM sub-partition as well.  B = 4 096: evaluation launches 192 -> 177 ms per batch; unrolling the four
+    // stages on top of it: 178 ms.)
+    if constexpr (MODEL == MPCB_MODEL_PACEJKA6) M::template call_spec<true>(sq, su, v, kp, kq, L);
+    else M::template call<true>(sq, su, v, kp, kq, L);
     accp[0] = fma(bw, kp[0], accp[0]);
     accp[1] = fma(bw, kp[1], accp[1]);
 #pragma unroll
