@@ -65,3 +65,23 @@ def test_product_never_imports_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 for pat in pats:
                     assert not re.search(pat, src, flags=re.M), f"{f} matches {pat}: product must not use the oracle"
+
+
+def test_dedupe_roads_host_logic():
+    """alpaqa_compat.dedupe_roads: per-instance centerlines that take a few distinct values become a road table + index
+    (the shared-memory pruned scan), anything else stays per-instance (None)."""
+    import numpy as np
+    from mpcb200 import alpaqa_compat as pa
+    rng = np.random.default_rng(0)
+    t = rng.normal(size=(3, 40))
+    idx = rng.integers(0, 3, 500)
+    table, got = pa.dedupe_roads(t[idx])
+    assert table.shape[0] == 3 and got.dtype == np.int32
+    assert np.array_equal(table[got], t[idx])                       # every row maps to its own road
+    assert np.array_equal(table[0], t[idx[0]])                      # roads are numbered by first appearance
+    one, i1 = pa.dedupe_roads(np.tile(t[1], (7, 1)))
+    assert one.shape == (1, 40) and (i1 == 0).all()
+    assert pa.dedupe_roads(rng.normal(size=(pa.MAX_TABLE_ROADS + 1, 40))) is None   # too many distinct roads
+    bad = np.tile(t[0], (4, 1))
+    bad[2, 5] = np.nan                                              # a NaN row equals nothing, not even itself
+    assert pa.dedupe_roads(np.tile(bad, (pa.MAX_TABLE_ROADS + 1, 1))) is None
